@@ -1,0 +1,335 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the attention hot path (BASELINE.json metric
+"paged-attn decode HBM GB/s").
+
+Workload (config.workload): BASELINE.json configs[2], the configuration the decode metric is
+quoted on and the largest that fits one GPU: Qwen3-8B decode-heavy paged attention, 512
+sequences at 4096-token context, GQA 32q/8kv, page 256, bf16.  One "step" = one pass of the hot
+path over one decode batch of one layer through the drop-in `Attention.forward`: KV scatter of
+the 512 new tokens by slot_mapping, then split-K paged decode attention over the cache.
+At N GPUs the heads shard exactly as the reference's tensor parallelism shards them
+(TP=N: Hq/N query heads and Hkv/N KV heads per rank, no collective on this path); total work is
+fixed, so "scaling" is "strong" and `value` = bytes all ranks processed / max-over-ranks time.
+
+  value ......... algorithmic GB/s, inputs resident in HBM, CUDA events, max over ranks
+  e2e ........... same metric through the public API with HOST (pinned) q/k/v/metadata copied
+                  in and the output copied out inside the timed region (KV cache stays resident:
+                  it is persistent device state in the reference too, model_runner.py:368)
+  roofline ...... paged_decode_kernel alone, timed live with CUDA events on its stream
+  cpu_baseline .. the CPU oracle port (pure torch, all host threads) on a bounded sample
+
+`--impl reference` times that CPU port alone (the reference has no CPU implementation of this
+path: its Triton + flash-attn kernels are CUDA-only), as the contract's reference arm.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "nano-vllm-v1_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import torch  # noqa: E402
+
+B, CTX, HQ, HKV, D, PAGE = 512, 4096, 32, 8, 128, 256
+WORKLOAD = "qwen3-8b-decode-paged-attn-b512-ctx4096-gqa32q8kv"
+METRIC = "paged_attn_decode_hbm_gbps"
+
+
+def algorithmic_bytes(batch, ctx, hq, hkv):
+    """SURVEY.md 8(d).  decode: sum_b (2*Lk*Hkv*D + 2*Hq*D) * 2 B ; scatter: T*(4*Hkv*D*2 + 4) B."""
+    decode = batch * (2 * ctx * hkv * D + 2 * hq * D) * 2
+    scatter = batch * (4 * hkv * D * 2 + 4)
+    return decode, scatter
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, copy burst)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock + throttle reasons during the timed region (NVML, 100 ms)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop_evt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.ok = False
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop_evt.wait(0.1)
+
+    def finish(self):
+        self._stop_evt.set()
+        if self.is_alive():
+            self.join(timeout=2)
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def build_problem(rank, world, device, seed=0):
+    """Per-rank shard of cfg3: every sequence owns 16 distinct pages drawn from a seeded
+    permutation; cache values N(0,1) bf16."""
+    hq, hkv = HQ // world, HKV // world
+    nblk = B * (CTX // PAGE)
+    g = torch.Generator(device=device).manual_seed(seed + rank)
+    k_cache = torch.randn(nblk, PAGE, hkv, D, generator=g, device=device, dtype=torch.bfloat16)
+    v_cache = torch.randn(nblk, PAGE, hkv, D, generator=g, device=device, dtype=torch.bfloat16)
+    perm = torch.randperm(nblk, generator=torch.Generator().manual_seed(seed)).to(torch.int32)
+    block_tables = perm.view(B, CTX // PAGE).contiguous()
+    context_lens = torch.full((B,), CTX, dtype=torch.int32)
+    # the token decoded this step sits at position CTX-1 of every sequence
+    slot_mapping = (block_tables[:, -1].to(torch.int64) * PAGE + (CTX - 1) % PAGE).to(torch.int32)
+    gq = torch.Generator().manual_seed(seed + 1000 + rank)
+    qkv = torch.randn(B, (hq + 2 * hkv) * D, generator=gq).bfloat16()
+    return dict(hq=hq, hkv=hkv, k_cache=k_cache, v_cache=v_cache, block_tables=block_tables,
+                context_lens=context_lens, slot_mapping=slot_mapping, qkv=qkv)
+
+
+def split_qkv(qkv, hq, hkv):
+    q, k, v = qkv.split([hq * D, hkv * D, hkv * D], dim=-1)
+    T = qkv.shape[0]
+    return q.view(T, hq, D), k.view(T, hkv, D), v.view(T, hkv, D)      # v (and here q,k) strided views of qkv
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    import b200attn
+    from b200attn import ops
+    from b200attn.layers.attention import Attention
+    from b200attn.utils.context import reset_context, set_context
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}"
+    assert HKV % world == 0
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    b200attn.load_library()
+
+    pr = build_problem(rank, world, device)
+    hq, hkv = pr["hq"], pr["hkv"]
+    scale = D ** -0.5
+    attn = Attention(hq, D, scale, hkv)
+    attn.k_cache, attn.v_cache = pr["k_cache"], pr["v_cache"]
+    bt_d, cl_d, sm_d = pr["block_tables"].to(device), pr["context_lens"].to(device), pr["slot_mapping"].to(device)
+    qkv_d = pr["qkv"].to(device)
+    q_d, k_d, v_d = split_qkv(qkv_d, hq, hkv)
+    q_c, k_c = q_d.contiguous(), k_d.contiguous()                     # RoPE output is contiguous
+    num_splits = b200attn.load_library().b200_decode_plan(B, hkv, bt_d.shape[1] * PAGE)
+    ops.reserve_decode_workspace(B, hq, hkv, bt_d.shape[1] * PAGE, device)
+
+    def step_resident():
+        set_context(None, None, 0, 0, sm_d, cl_d, bt_d, None)       # graph-decode form (attention.py:222)
+        return attn(q_c, k_c, v_d)
+
+    # pinned host staging for the e2e leg
+    pin = lambda t: t.clone().pin_memory()  # noqa: E731
+    h_qkv, h_sm, h_cl, h_bt = pin(pr["qkv"]), pin(pr["slot_mapping"]), pin(pr["context_lens"]), pin(pr["block_tables"])
+    h_out = torch.empty(B, hq, D, dtype=torch.bfloat16).pin_memory()
+    d_qkv, d_sm, d_cl, d_bt = (torch.empty_like(t, device=device) for t in (h_qkv, h_sm, h_cl, h_bt))
+    h2d = sum(t.numel() * t.element_size() for t in (h_qkv, h_sm, h_cl, h_bt))
+    d2h = h_out.numel() * h_out.element_size()
+
+    def step_e2e():
+        d_qkv.copy_(h_qkv, non_blocking=True)
+        d_sm.copy_(h_sm, non_blocking=True)
+        d_cl.copy_(h_cl, non_blocking=True)
+        d_bt.copy_(h_bt, non_blocking=True)
+        q, k, v = split_qkv(d_qkv, hq, hkv)
+        set_context(None, None, 0, 0, d_sm, d_cl, d_bt, None)
+        o = attn(q, k, v)
+        h_out.copy_(o, non_blocking=True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=device, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = t.item()
+        return ms
+
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+        step_e2e()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms_total = timed(step_resident, args.steps)
+    clocks = sampler.finish()
+    ms_e2e = timed(step_e2e, args.steps)
+
+    # dominant kernel alone (paged_decode_kernel [+ reduce when split]) on the launching stream
+    def decode_only():
+        ops.attn_decode(q_c, attn.k_cache, attn.v_cache, cl_d, bt_d, scale, num_splits=num_splits)
+    for _ in range(3):
+        decode_only()
+    ms_decode = timed(decode_only, args.steps) / args.steps
+    reset_context()
+
+    dec_b, sc_b = algorithmic_bytes(B, CTX, hq, hkv)
+    total_bytes = (dec_b + sc_b) * world
+    ms_step = ms_total / args.steps
+    value = total_bytes / (ms_step * 1e-3) / 1e9
+    e2e_value = total_bytes / (ms_e2e / args.steps * 1e-3) / 1e9
+    peak, peak_src = peaks()
+    achieved = dec_b / (ms_decode * 1e-3) / 1e9                      # per GPU
+    launches_per_step = 2 + (1 if num_splits > 1 else 0)
+
+    if rank == 0:
+        cpu = cpu_baseline_sample() if world == 1 and not args.no_cpu_baseline else None
+        traffic = None
+        try:
+            with open(os.path.join(ROOT, "profiles", "decode_traffic.json")) as f:
+                traffic = json.load(f).get("dram_bytes_per_launch")
+        except Exception:
+            pass
+        line = {
+            "metric": METRIC, "value": round(value, 1), "unit": "GB/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": round(ms_step, 4), "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "batch": B, "context_len": CTX, "q_heads": HQ, "kv_heads": HKV,
+                       "head_dim": D, "page": PAGE, "sharding": f"tp{world} (heads; no collective on this path)",
+                       "step": "Attention.forward = kv_scatter + paged decode (+reduce)", "num_splits": num_splits,
+                       "l2": "inputs larger than L2 (K/V working set %.2f GB per GPU vs 126 MB L2)" % (dec_b / 1e9)},
+            "e2e": {"value": round(e2e_value, 1), "unit": "GB/s", "h2d_bytes_per_step": h2d * world,
+                    "d2h_bytes_per_step": d2h * world, "ms_per_step": round(ms_e2e / args.steps, 4)},
+            "gpu_launches": launches_per_step * args.steps,
+            "roofline": {"kernel": "paged_decode_kernel", "bound": "hbm", "achieved": round(achieved, 1),
+                         "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic,
+                         "peak_source": peak_src, "algorithmic_bytes_per_launch": dec_b,
+                         "ms_per_launch": round(ms_decode, 4), "frac_of_nominal_8TBps": round(achieved / 8000.0, 4)},
+            "cpu_baseline": cpu,
+            "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_baseline_sample(num_seqs=32, reps=2):
+    """The oracle (port of the reference semantics; the reference has no CPU path) on a bounded
+    sample: `num_seqs` of the 512 sequences, full 4096-token context, 32q/8kv, all host threads."""
+    import oracle
+    torch.set_num_threads(os.cpu_count() or 1)
+    g = torch.Generator().manual_seed(0)
+    nblk = num_seqs * (CTX // PAGE)
+    kc = torch.randn(nblk, PAGE, HKV, D, generator=g).bfloat16()
+    vc = torch.randn(nblk, PAGE, HKV, D, generator=g).bfloat16()
+    bt = torch.randperm(nblk, generator=g).to(torch.int32).view(num_seqs, -1)
+    cl = torch.full((num_seqs,), CTX, dtype=torch.int32)
+    slot = (bt[:, -1].to(torch.int64) * PAGE + (CTX - 1) % PAGE).to(torch.int32)
+    q = torch.randn(num_seqs, HQ, D, generator=g).bfloat16()
+    k = torch.randn(num_seqs, HKV, D, generator=g).bfloat16()
+    v = torch.randn(num_seqs, HKV, D, generator=g).bfloat16()
+    ctx = oracle.Context(None, None, 0, 0, slot, cl, bt, None)
+    oracle.attention_forward(q[:2], k[:2], v[:2], kc, vc, oracle.Context(None, None, 0, 0, slot[:2], cl[:2], bt[:2], None), D ** -0.5)
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        oracle.attention_forward(q, k, v, kc, vc, ctx, D ** -0.5)
+    dt = (time.perf_counter() - t0) / reps
+    dec_b, sc_b = algorithmic_bytes(num_seqs, CTX, HQ, HKV)
+    return {"value": round((dec_b + sc_b) / dt / 1e9, 3), "unit": "GB/s", "cores": torch.get_num_threads(),
+            "kind": "port", "sample": f"{num_seqs} of {B} sequences x {CTX} ctx, 32q/8kv, {reps} reps, "
+                                      f"{dt:.2f} s per pass (oracle/paged_attention.py, torch CPU fp32)"}
+
+
+def run_reference(args):
+    """Reference arm: the reference's path has no CPU implementation (Triton + flash-attn are
+    CUDA-only), so this times the oracle port on the host cores.  Rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    num_seqs = 32
+    t_all = []
+    cpu = None
+    for i in range(max(args.warmup, 1) + args.steps):
+        t0 = time.perf_counter()
+        cpu = cpu_baseline_sample(num_seqs=num_seqs, reps=1)
+        if i >= max(args.warmup, 1):
+            t_all.append(cpu["value"])
+        if time.perf_counter() - t0 > 60:
+            break
+    val = sum(t_all) / max(len(t_all), 1) if t_all else (cpu["value"] if cpu else 0.0)
+    dec_b, sc_b = algorithmic_bytes(num_seqs, CTX, HQ, HKV)
+    cpu = dict(cpu or {}, value=round(val, 3))
+    line = {"impl": "reference", "metric": METRIC, "value": round(val, 3), "unit": "GB/s", "n_gpus": args.gpus,
+            "steps": len(t_all), "warmup": max(args.warmup, 1), "ms_per_step": round((dec_b + sc_b) / max(val, 1e-9) / 1e6, 3),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16 in / fp32 math",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "batch": B, "context_len": CTX, "q_heads": HQ, "kv_heads": HKV,
+                       "head_dim": D, "page": PAGE, "sample": cpu.get("sample")},
+            "cpu_baseline": cpu,
+            "e2e": {"value": round(val, 3), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,139 @@
+/*
+ * b200attn.h -- C ABI of the B200-native attention hot path for nano-vllm-v1.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no torch types, no C++
+ * exceptions.  The reference is pure Python; what it binds for this path today are
+ * (a) a Triton kernel and (b) two flash-attn entry points plus three inductor-compiled
+ * pointwise modules.  Each function below names the reference interface it replaces.
+ * A maintainer binds them with ctypes (INTEGRATION.md shows the stub); the shipped
+ * host-side mirror is nano-vllm-v1_b200/b200attn/.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host;
+ *   - element type is bf16 (2 bytes) for q/k/v/caches/out, int32 for index arrays,
+ *     int64 for positions, fp32 for the RoPE cache (the reference's own dtypes,
+ *     SURVEY.md 2.4); head_dim must be 128 and the KV page 256 tokens;
+ *   - *_stride arguments are in ELEMENTS; inner (head_dim) stride is 1 and the head
+ *     stride is head_dim, exactly what attention.py:121-122 asserts;
+ *   - `stream` is a cudaStream_t passed as void*; all work is stream-ordered, nothing is
+ *     allocated, freed or retained, no host synchronisation happens inside;
+ *   - return value: 0 = ok; negative = argument error (B200_ERR_*); positive = cudaError_t
+ *     of a failed launch.  b200_status_string() describes either.
+ *   - graph-capture safe: every length is read from device memory; launch geometry
+ *     depends only on host integers.
+ */
+#ifndef B200ATTN_H_
+#define B200ATTN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200ATTN_VERSION 100 /* 0.1.0 */
+
+#define B200_OK 0
+#define B200_ERR_NULL (-1)       /* required pointer is NULL */
+#define B200_ERR_SHAPE (-2)      /* unsupported head_dim / page size / head counts */
+#define B200_ERR_ALIGN (-3)      /* pointer or stride not 16-byte aligned */
+#define B200_ERR_WORKSPACE (-4)  /* workspace too small for (batch, heads, splits) */
+#define B200_ERR_RANGE (-5)      /* negative or overflowing count */
+#define B200_ERR_UNAVAILABLE (-6)/* requested kernel variant not built / no driver entry point */
+
+int b200_version(void);
+const char* b200_status_string(int status);
+
+/* Number of SMs of the current device (cached); helper for split planning. */
+int b200_sm_count(void);
+
+/* ---------------------------------------------------------------------------------
+ * (1) KV-cache scatter.  Replaces store_kvcache_kernel + store_kvcache,
+ *     nanovllm/layers/attention.py:34-90 and :93-127.
+ *     k_cache.view(-1, Hkv*D)[slot_mapping[i]] = key[i]; same for value; slot -1 skipped.
+ *     key/value: [T, Hkv, D] with row strides (value is a strided view of qkv).
+ *     Bit-exact copy; 64-bit addressing (the Triton kernel's 32-bit `slot * D` is not kept).
+ */
+int b200_kv_scatter(const void* key, const void* value,
+                    int64_t key_row_stride, int64_t value_row_stride,
+                    void* k_cache, void* v_cache, const int32_t* slot_mapping,
+                    int32_t num_tokens, int32_t num_kv_heads, int32_t head_dim,
+                    void* stream);
+
+/* ---------------------------------------------------------------------------------
+ * (3) Paged decode attention (split-K + reduce).  Replaces flash_attn_with_kvcache as
+ *     called at attention.py:229-232, and flash_attn_varlen_func (attention.py:242-248)
+ *     for batches whose every row has one query token (eager decode).
+ *     q/out: [B, Hq, D] (token stride given); caches [num_blocks, 256, Hkv, D];
+ *     context_lens int32[B] (0 => row is graph padding, output 0);
+ *     block_tables int32[B, >=ceil(len/256)] with row stride bt_row_stride; entries past
+ *     the context (-1 eager, 0 graph) are never dereferenced.
+ *     num_splits: from b200_decode_plan (host-only heuristic => static under CUDA graphs).
+ *     workspace: b200_decode_workspace_bytes(B, Hq, num_splits) bytes, may be NULL iff
+ *     num_splits == 1.
+ */
+int b200_decode_plan(int32_t batch, int32_t num_kv_heads, int32_t max_context_len);
+size_t b200_decode_workspace_bytes(int32_t batch, int32_t num_heads, int32_t num_splits);
+int b200_attn_decode(const void* q, int64_t q_token_stride,
+                     const void* k_cache, const void* v_cache,
+                     void* out, int64_t out_token_stride,
+                     const int32_t* context_lens,
+                     const int32_t* block_tables, int32_t bt_row_stride,
+                     int32_t batch, int32_t num_heads, int32_t num_kv_heads,
+                     int32_t head_dim, int32_t page_size, float softmax_scale,
+                     int32_t num_splits, void* workspace, size_t workspace_bytes,
+                     void* stream);
+
+/* ---------------------------------------------------------------------------------
+ * (2) Varlen causal prefill / chunked-prefill attention.  Replaces
+ *     flash_attn_varlen_func as called at attention.py:242-248:
+ *       block_tables == NULL : k, v are packed [Tk, Hkv, D] with token strides
+ *                              (sub-paths A/B of SURVEY 3.4; v is a strided view);
+ *       block_tables != NULL : k, v are the caches [num_blocks, 256, Hkv, D]
+ *                              (token strides ignored), rows gathered through the table.
+ *     Bottom-right aligned causal mask (query i sees keys j <= i + Lk - Lq).
+ *     cu_seqlens_q/k int32[B+1] on device; max_seqlen_q/k host ints as in the reference.
+ *     variant: 0 = auto, 1 = mma.sync kernel, 2 = tcgen05/TMEM/TMA kernel.
+ */
+int b200_attn_prefill(const void* q, int64_t q_token_stride,
+                      const void* k, const void* v,
+                      int64_t k_token_stride, int64_t v_token_stride,
+                      void* out, int64_t out_token_stride,
+                      const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
+                      const int32_t* block_tables, int32_t bt_row_stride,
+                      int32_t batch, int32_t total_q, int32_t max_seqlen_q, int32_t max_seqlen_k,
+                      int32_t num_heads, int32_t num_kv_heads, int32_t head_dim,
+                      int32_t page_size, int64_t num_cache_blocks, float softmax_scale,
+                      int32_t variant, void* stream);
+
+/* ---------------------------------------------------------------------------------
+ * (4a) Fused per-head RMSNorm + RoPE on q and k.  Replaces q_norm/k_norm
+ *      (layers/layernorm.py:57-93 via models/qwen3.py:191-193) followed by
+ *      RotaryEmbedding.forward (layers/rotary_embedding.py:114-153), keeping the two
+ *      bf16 roundings between them.  q [T,Hq,D], k [T,Hkv,D] are views with token strides;
+ *      q_out/k_out are contiguous [T,H,D]; positions int64[T]; cos_sin fp32 [max_pos, D].
+ *      q_weight / k_weight NULL => that tensor is only rotated (stand-alone RotaryEmbedding.forward).
+ */
+int b200_qk_norm_rope(const void* q, int64_t q_token_stride,
+                      const void* k, int64_t k_token_stride,
+                      const int64_t* positions, const float* cos_sin_cache,
+                      const void* q_weight, const void* k_weight, float eps,
+                      void* q_out, void* k_out,
+                      int32_t num_tokens, int32_t num_heads, int32_t num_kv_heads,
+                      int32_t head_dim, void* stream);
+
+/* (4a') RMSNorm over the hidden size with optional fused residual add.  Replaces
+ *      RMSNorm.rms_forward / add_rms_forward (layernorm.py:57-141).  residual may be NULL;
+ *      when given it is updated IN PLACE to round(x + residual), as the reference returns. */
+int b200_rmsnorm(const void* x, void* residual, const void* weight, float eps,
+                 void* out, int32_t num_tokens, int32_t hidden, void* stream);
+
+/* (4b) SiluAndMul.  Replaces layers/activation.py:36-58: out[T,I] = silu(x[:, :I]) * x[:, I:],
+ *      fp32 math, one rounding (the compiled form the reference runs on the GPU). */
+int b200_silu_and_mul(const void* x, void* out, int32_t num_tokens, int32_t inter, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200ATTN_H_ */

@@ -1,0 +1,213 @@
+"""Tensor-level wrappers: validate like the reference does, pass raw pointers to the C ABI.
+
+PyTorch is plumbing only here (device memory, the current stream, output allocation).
+Error conventions follow the reference: layout problems are `AssertionError`s
+(nanovllm/layers/attention.py:121-124), wrong dtype/device `RuntimeError`s (flash-attn's
+TORCH_CHECKs).
+"""
+from typing import Optional, Tuple
+
+import torch
+
+from ._lib import check, load_library
+
+PAGE = 256
+HEAD_DIM = 128
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _need_cuda_bf16(t: torch.Tensor, name: str) -> None:
+    if not t.is_cuda:
+        raise RuntimeError(f"b200attn: {name} must be a CUDA tensor (no CPU fallback on this path)")
+    if t.dtype != torch.bfloat16:
+        raise RuntimeError(f"b200attn: {name} must be bfloat16, got {t.dtype}")
+
+
+def _need_i32(t: torch.Tensor, name: str) -> None:
+    if not t.is_cuda or t.dtype != torch.int32:
+        raise RuntimeError(f"b200attn: {name} must be a CUDA int32 tensor")
+    assert t.is_contiguous() or t.dim() == 2 and t.stride(1) == 1, f"{name} must be contiguous"
+
+
+# ------------------------------------------------------------------------------------ (1)
+def store_kvcache(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                  slot_mapping: torch.Tensor) -> None:
+    """Same contract as nanovllm.layers.attention.store_kvcache (attention.py:93-127)."""
+    N, num_heads, head_dim = key.shape
+    D = num_heads * head_dim
+    assert key.stride(-1) == 1 and value.stride(-1) == 1
+    assert key.stride(1) == head_dim and value.stride(1) == head_dim
+    assert k_cache.stride(1) == D and v_cache.stride(1) == D
+    assert slot_mapping.numel() == N
+    for t, n in ((key, "key"), (value, "value"), (k_cache, "k_cache"), (v_cache, "v_cache")):
+        _need_cuda_bf16(t, n)
+    _need_i32(slot_mapping, "slot_mapping")
+    lib = load_library()
+    check(lib.b200_kv_scatter(key.data_ptr(), value.data_ptr(), key.stride(0), value.stride(0),
+                              k_cache.data_ptr(), v_cache.data_ptr(), slot_mapping.data_ptr(),
+                              N, num_heads, head_dim, _stream()), "b200_kv_scatter")
+
+
+# ------------------------------------------------------------------------------------ (3)
+class DecodeWorkspace:
+    """Split-K partials, allocated once (allocate_kv_cache time) and reused by every layer."""
+
+    def __init__(self, max_batch: int, num_heads: int, max_splits: int, device) -> None:
+        lib = load_library()
+        self.max_batch, self.num_heads, self.max_splits = max_batch, num_heads, max_splits
+        nbytes = lib.b200_decode_workspace_bytes(max_batch, num_heads, max(max_splits, 2))
+        self.buf = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=device)
+
+    def fits(self, batch: int, num_heads: int, splits: int) -> bool:
+        return load_library().b200_decode_workspace_bytes(batch, num_heads, splits) <= self.buf.numel()
+
+
+_WS_CACHE = {}
+
+
+def _workspace_for(batch: int, num_heads: int, splits: int, device) -> Optional[torch.Tensor]:
+    if splits <= 1:
+        return None
+    key = (device.index if device.index is not None else torch.cuda.current_device())
+    ws = _WS_CACHE.get(key)
+    need = load_library().b200_decode_workspace_bytes(batch, num_heads, splits)
+    if ws is None or ws.numel() < need:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("b200attn: decode workspace must be sized before CUDA-graph capture "
+                               "(call ops.reserve_decode_workspace first)")
+        ws = torch.empty(int(need * 1.25) + 256, dtype=torch.uint8, device=device)
+        _WS_CACHE[key] = ws
+    return ws
+
+
+def reserve_decode_workspace(max_batch: int, num_heads: int, num_kv_heads: int, max_context: int, device) -> None:
+    """Size the per-device split-K workspace for the worst graph bucket (call before capture)."""
+    lib = load_library()
+    worst = 0
+    bs = 1
+    cands = sorted({1, 2, 4, 8, *range(16, max_batch + 1, 16), max_batch})
+    for bs in cands:
+        s = lib.b200_decode_plan(bs, num_kv_heads, max_context)
+        worst = max(worst, lib.b200_decode_workspace_bytes(bs, num_heads, s))
+    key = (torch.device(device).index if torch.device(device).index is not None else torch.cuda.current_device())
+    cur = _WS_CACHE.get(key)
+    if cur is None or cur.numel() < worst:
+        _WS_CACHE[key] = torch.empty(worst + 256, dtype=torch.uint8, device=device)
+
+
+def attn_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, context_lens: torch.Tensor,
+                block_tables: torch.Tensor, scale: float, num_splits: Optional[int] = None,
+                out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """q [B, Hq, D] -> [B, Hq, D].  Semantics of flash_attn_with_kvcache at attention.py:229-232."""
+    B, Hq, D = q.shape
+    Hkv = k_cache.shape[2]
+    for t, n in ((q, "q"), (k_cache, "k_cache"), (v_cache, "v_cache")):
+        _need_cuda_bf16(t, n)
+    _need_i32(context_lens, "context_lens")
+    _need_i32(block_tables, "block_tables")
+    assert q.stride(-1) == 1 and q.stride(1) == D
+    assert k_cache.is_contiguous() and v_cache.is_contiguous() and k_cache.shape[1] == PAGE
+    assert block_tables.shape[0] == B and context_lens.numel() == B
+    lib = load_library()
+    if num_splits is None:
+        num_splits = lib.b200_decode_plan(B, Hkv, block_tables.shape[1] * PAGE)
+    ws = _workspace_for(B, Hq, num_splits, q.device)
+    if out is None:
+        out = torch.empty((B, Hq, D), dtype=q.dtype, device=q.device)
+    check(lib.b200_attn_decode(q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(),
+                               out.data_ptr(), out.stride(0), context_lens.data_ptr(),
+                               block_tables.data_ptr(), block_tables.stride(0), B, Hq, Hkv, D, PAGE,
+                               float(scale), num_splits, ws.data_ptr() if ws is not None else None,
+                               ws.numel() if ws is not None else 0, _stream()), "b200_attn_decode")
+    return out
+
+
+# ------------------------------------------------------------------------------------ (2)
+def attn_varlen(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens_q: torch.Tensor,
+                cu_seqlens_k: torch.Tensor, max_seqlen_q: int, max_seqlen_k: int, scale: float,
+                block_table: Optional[torch.Tensor] = None, variant: int = 0,
+                out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Semantics of flash_attn_varlen_func(..., causal=True, block_table=...) at attention.py:242-248."""
+    T, Hq, D = q.shape
+    for t, n in ((q, "q"), (k, "k"), (v, "v")):
+        _need_cuda_bf16(t, n)
+    _need_i32(cu_seqlens_q, "cu_seqlens_q")
+    _need_i32(cu_seqlens_k, "cu_seqlens_k")
+    assert q.stride(-1) == 1 and q.stride(1) == D
+    B = cu_seqlens_q.numel() - 1
+    assert cu_seqlens_k.numel() == B + 1
+    if block_table is not None:
+        _need_i32(block_table, "block_table")
+        assert k.dim() == 4 and k.is_contiguous() and v.is_contiguous() and k.shape[1] == PAGE
+        Hkv = k.shape[2]
+        ks = vs = 0
+        nblocks = k.shape[0]
+        bt_ptr, bt_stride = block_table.data_ptr(), block_table.stride(0)
+        assert block_table.shape[0] == B
+    else:
+        assert k.dim() == 3 and k.stride(-1) == 1 and v.stride(-1) == 1
+        assert k.stride(1) == D and v.stride(1) == D
+        Hkv = k.shape[1]
+        ks, vs = k.stride(0), v.stride(0)
+        nblocks = 0
+        bt_ptr, bt_stride = None, 0
+    if out is None:
+        out = torch.empty((T, Hq, D), dtype=q.dtype, device=q.device)
+    lib = load_library()
+    check(lib.b200_attn_prefill(q.data_ptr(), q.stride(0), k.data_ptr(), v.data_ptr(), ks, vs,
+                                out.data_ptr(), out.stride(0), cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr(),
+                                bt_ptr, bt_stride, B, T, int(max_seqlen_q), int(max_seqlen_k), Hq, Hkv, D, PAGE,
+                                nblocks, float(scale), variant, _stream()), "b200_attn_prefill")
+    return out
+
+
+# ------------------------------------------------------------------------------------ (4)
+def qk_norm_rope(q: torch.Tensor, k: torch.Tensor, positions: torch.Tensor, q_weight: Optional[torch.Tensor],
+                 k_weight: Optional[torch.Tensor], cos_sin_cache: torch.Tensor, eps: float = 1e-6) -> Tuple[torch.Tensor, torch.Tensor]:
+    """q [T,Hq,128], k [T,Hkv,128] (views of qkv) -> fresh contiguous (q', k'); qwen3.py:191-195."""
+    T, Hq, D = q.shape
+    Hkv = k.shape[1]
+    _need_cuda_bf16(q, "q")
+    _need_cuda_bf16(k, "k")
+    assert q.stride(-1) == 1 and q.stride(1) == D and k.stride(-1) == 1 and k.stride(1) == D
+    assert positions.dtype == torch.int64 and positions.is_cuda and positions.is_contiguous()
+    assert cos_sin_cache.dtype == torch.float32 and cos_sin_cache.is_contiguous() and cos_sin_cache.shape[-1] == D
+    q_out = torch.empty((T, Hq, D), dtype=q.dtype, device=q.device)
+    k_out = torch.empty((T, Hkv, D), dtype=k.dtype, device=k.device)
+    check(load_library().b200_qk_norm_rope(q.data_ptr(), q.stride(0), k.data_ptr(), k.stride(0),
+                                           positions.data_ptr(), cos_sin_cache.data_ptr(),
+                                           q_weight.data_ptr() if q_weight is not None else None,
+                                           k_weight.data_ptr() if k_weight is not None else None, float(eps), q_out.data_ptr(), k_out.data_ptr(),
+                                           T, Hq, Hkv, D, _stream()), "b200_qk_norm_rope")
+    return q_out, k_out
+
+
+def rms_norm(x: torch.Tensor, weight: torch.Tensor, eps: float, residual: Optional[torch.Tensor] = None):
+    """layernorm.py:143-165.  With `residual`, returns (normed, residual_out) like the reference;
+    residual is updated in place."""
+    _need_cuda_bf16(x, "x")
+    assert x.is_contiguous()
+    hidden = x.shape[-1]
+    T = x.numel() // hidden
+    out = torch.empty_like(x)
+    if residual is not None:
+        _need_cuda_bf16(residual, "residual")
+        assert residual.is_contiguous() and residual.shape == x.shape
+    check(load_library().b200_rmsnorm(x.data_ptr(), residual.data_ptr() if residual is not None else None,
+                                      weight.data_ptr(), float(eps), out.data_ptr(), T, hidden, _stream()),
+          "b200_rmsnorm")
+    return out if residual is None else (out, residual)
+
+
+def silu_and_mul(x: torch.Tensor) -> torch.Tensor:
+    """activation.py:36-58: [.., 2I] -> [.., I]."""
+    _need_cuda_bf16(x, "x")
+    assert x.is_contiguous() and x.shape[-1] % 2 == 0
+    inter = x.shape[-1] // 2
+    T = x.numel() // (2 * inter)
+    out = torch.empty(x.shape[:-1] + (inter,), dtype=x.dtype, device=x.device)
+    check(load_library().b200_silu_and_mul(x.data_ptr(), out.data_ptr(), T, inter, _stream()), "b200_silu_and_mul")
+    return out

@@ -1,0 +1,192 @@
+// extern "C" surface declared in include/b200attn.h: argument validation + dispatch.
+// No torch headers, no exceptions across the boundary, no allocation, no host sync.
+#include "../../include/b200attn.h"
+
+#include <cuda_runtime.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "launch.h"
+
+namespace b200 {
+int sm_count() {
+    static int cached = 0;
+    if (cached == 0) {
+        int dev = 0, n = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess ||
+            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+            n = 148;                                              // B200
+        cached = n;
+    }
+    return cached;
+}
+}  // namespace b200
+
+using namespace b200;
+
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+static inline bool stride_ok(int64_t elems) { return ((elems * 2) & 15) == 0; }
+
+extern "C" {
+
+int b200_version(void) { return B200ATTN_VERSION; }
+
+const char* b200_status_string(int status) {
+    switch (status) {
+        case B200_OK: return "ok";
+        case B200_ERR_NULL: return "b200attn: required pointer is NULL";
+        case B200_ERR_SHAPE: return "b200attn: unsupported shape (need head_dim 128, page 256, Hq % Hkv == 0, Hq/Hkv <= 16)";
+        case B200_ERR_ALIGN: return "b200attn: pointer or stride not 16-byte aligned";
+        case B200_ERR_WORKSPACE: return "b200attn: split-K workspace too small";
+        case B200_ERR_RANGE: return "b200attn: negative or out-of-range count";
+        case B200_ERR_UNAVAILABLE: return "b200attn: requested kernel variant unavailable";
+        default: break;
+    }
+    if (status > 0) return cudaGetErrorString(static_cast<cudaError_t>(status));
+    return "b200attn: unknown status";
+}
+
+int b200_sm_count(void) { return sm_count(); }
+
+int b200_kv_scatter(const void* key, const void* value, int64_t key_row_stride, int64_t value_row_stride,
+                    void* k_cache, void* v_cache, const int32_t* slot_mapping,
+                    int32_t num_tokens, int32_t num_kv_heads, int32_t head_dim, void* stream) {
+    if (num_tokens < 0 || num_kv_heads <= 0) return B200_ERR_RANGE;
+    if (num_tokens == 0) return B200_OK;
+    if (!key || !value || !k_cache || !v_cache || !slot_mapping) return B200_ERR_NULL;
+    if (head_dim != B200_HD_CONST) return B200_ERR_SHAPE;
+    if (!aligned16(key) || !aligned16(value) || !aligned16(k_cache) || !aligned16(v_cache) ||
+        !stride_ok(key_row_stride) || !stride_ok(value_row_stride))
+        return B200_ERR_ALIGN;
+    return launch_kv_scatter(key, value, key_row_stride, value_row_stride, k_cache, v_cache, slot_mapping,
+                             num_tokens, num_kv_heads, head_dim, (cudaStream_t)stream);
+}
+
+// Host-only heuristic (static under CUDA graphs, like flash-attn's num_splits which is fixed at
+// capture time): smallest split count whose grid fills >= 90 % of its last wave, never finer
+// than one page per split.
+int b200_decode_plan(int32_t batch, int32_t num_kv_heads, int32_t max_context_len) {
+    if (batch <= 0 || num_kv_heads <= 0) return 1;
+    const char* env = getenv("B200ATTN_DECODE_SPLITS");
+    if (env && atoi(env) > 0) return atoi(env);
+    const int64_t slots = (int64_t)sm_count() * 2;               // 2 resident CTAs per SM
+    const int64_t items = (int64_t)batch * num_kv_heads;
+    if (items >= slots * 4) return 1;
+    int cap = (max_context_len + 255) / 256;
+    if (cap < 1) cap = 1;
+    if (cap > 64) cap = 64;
+    int best = 1;
+    double best_eff = 0.0;
+    for (int s = 1; s <= cap; ++s) {
+        const int64_t ctas = items * s;
+        const int64_t waves = (ctas + slots - 1) / slots;
+        const double eff = (double)ctas / (double)(waves * slots);
+        if (eff > best_eff + 1e-9) { best_eff = eff; best = s; }
+        if (eff >= 0.90) { best = s; break; }
+    }
+    return best;
+}
+
+size_t b200_decode_workspace_bytes(int32_t batch, int32_t num_heads, int32_t num_splits) {
+    if (num_splits <= 1 || batch <= 0 || num_heads <= 0) return 0;
+    return (size_t)batch * num_splits * num_heads * (B200_HD_CONST + 1) * sizeof(float);
+}
+
+int b200_attn_decode(const void* q, int64_t q_token_stride, const void* k_cache, const void* v_cache,
+                     void* out, int64_t out_token_stride, const int32_t* context_lens,
+                     const int32_t* block_tables, int32_t bt_row_stride,
+                     int32_t batch, int32_t num_heads, int32_t num_kv_heads, int32_t head_dim, int32_t page_size,
+                     float softmax_scale, int32_t num_splits, void* workspace, size_t workspace_bytes, void* stream) {
+    if (batch < 0 || num_splits < 1 || bt_row_stride < 0) return B200_ERR_RANGE;
+    if (batch == 0) return B200_OK;
+    if (!q || !k_cache || !v_cache || !out || !context_lens || !block_tables) return B200_ERR_NULL;
+    if (head_dim != B200_HD_CONST || page_size != 256 || num_kv_heads <= 0 || num_heads % num_kv_heads != 0 ||
+        num_heads / num_kv_heads > 16)
+        return B200_ERR_SHAPE;
+    if (!aligned16(q) || !aligned16(k_cache) || !aligned16(v_cache) || !aligned16(out) ||
+        !stride_ok(q_token_stride) || !stride_ok(out_token_stride))
+        return B200_ERR_ALIGN;
+    const size_t need = b200_decode_workspace_bytes(batch, num_heads, num_splits);
+    if (num_splits > 1 && (!workspace || workspace_bytes < need)) return B200_ERR_WORKSPACE;
+    DecodeArgs a;
+    a.q = q; a.q_token_stride = q_token_stride; a.k_cache = k_cache; a.v_cache = v_cache;
+    a.out = out; a.out_token_stride = out_token_stride; a.context_lens = context_lens;
+    a.block_tables = block_tables; a.bt_row_stride = bt_row_stride;
+    a.batch = batch; a.Hq = num_heads; a.Hkv = num_kv_heads; a.scale = softmax_scale; a.num_splits = num_splits;
+    a.ws_o = (float*)workspace;
+    a.ws_lse = workspace ? (float*)workspace + (size_t)batch * num_splits * num_heads * B200_HD_CONST : nullptr;
+    return launch_attn_decode(a, (cudaStream_t)stream);
+}
+
+int b200_attn_prefill(const void* q, int64_t q_token_stride, const void* k, const void* v,
+                      int64_t k_token_stride, int64_t v_token_stride, void* out, int64_t out_token_stride,
+                      const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
+                      const int32_t* block_tables, int32_t bt_row_stride,
+                      int32_t batch, int32_t total_q, int32_t max_seqlen_q, int32_t max_seqlen_k,
+                      int32_t num_heads, int32_t num_kv_heads, int32_t head_dim, int32_t page_size,
+                      int64_t num_cache_blocks, float softmax_scale, int32_t variant, void* stream) {
+    if (batch < 0 || total_q < 0 || max_seqlen_q < 0 || max_seqlen_k < 0) return B200_ERR_RANGE;
+    if (batch == 0 || total_q == 0) return B200_OK;
+    if (!q || !k || !v || !out || !cu_seqlens_q || !cu_seqlens_k) return B200_ERR_NULL;
+    if (head_dim != B200_HD_CONST || (block_tables && page_size != 256) || num_kv_heads <= 0 ||
+        num_heads % num_kv_heads != 0)
+        return B200_ERR_SHAPE;
+    if (!aligned16(q) || !aligned16(k) || !aligned16(v) || !aligned16(out) || !stride_ok(q_token_stride) ||
+        !stride_ok(out_token_stride) || (!block_tables && (!stride_ok(k_token_stride) || !stride_ok(v_token_stride))))
+        return B200_ERR_ALIGN;
+    PrefillArgs a;
+    a.q = q; a.q_token_stride = q_token_stride; a.k = k; a.v = v;
+    a.k_token_stride = k_token_stride; a.v_token_stride = v_token_stride;
+    a.out = out; a.out_token_stride = out_token_stride; a.cu_q = cu_seqlens_q; a.cu_k = cu_seqlens_k;
+    a.block_tables = block_tables; a.bt_row_stride = bt_row_stride;
+    a.batch = batch; a.total_q = total_q; a.max_q = max_seqlen_q; a.max_k = max_seqlen_k;
+    a.Hq = num_heads; a.Hkv = num_kv_heads; a.num_cache_blocks = num_cache_blocks; a.scale = softmax_scale;
+    if (variant == 0) {
+        const char* env = getenv("B200ATTN_PREFILL");
+        if (env && !strcmp(env, "mma")) variant = 1;
+        else if (env && !strcmp(env, "tc")) variant = 2;
+        else variant = prefill_tc_available() ? 2 : 1;
+    }
+    if (variant == 2) {
+        if (!prefill_tc_available()) return B200_ERR_UNAVAILABLE;
+        return launch_attn_prefill_tc(a, (cudaStream_t)stream);
+    }
+    if (variant != 1) return B200_ERR_RANGE;
+    return launch_attn_prefill_mma(a, (cudaStream_t)stream);
+}
+
+int b200_qk_norm_rope(const void* q, int64_t q_token_stride, const void* k, int64_t k_token_stride,
+                      const int64_t* positions, const float* cos_sin_cache, const void* q_weight,
+                      const void* k_weight, float eps, void* q_out, void* k_out,
+                      int32_t num_tokens, int32_t num_heads, int32_t num_kv_heads, int32_t head_dim, void* stream) {
+    if (num_tokens < 0 || num_heads <= 0 || num_kv_heads <= 0) return B200_ERR_RANGE;
+    if (num_tokens == 0) return B200_OK;
+    if (!q || !k || !positions || !cos_sin_cache || !q_out || !k_out) return B200_ERR_NULL;   /* NULL weights => rotation only */
+    if (head_dim != B200_HD_CONST) return B200_ERR_SHAPE;
+    if ((reinterpret_cast<uintptr_t>(q) & 3) || (reinterpret_cast<uintptr_t>(k) & 3) || (q_token_stride & 1) ||
+        (k_token_stride & 1) || (reinterpret_cast<uintptr_t>(cos_sin_cache) & 7))
+        return B200_ERR_ALIGN;
+    return launch_qk_norm_rope(q, q_token_stride, k, k_token_stride, positions, cos_sin_cache, q_weight, k_weight,
+                               eps, q_out, k_out, num_tokens, num_heads, num_kv_heads, (cudaStream_t)stream);
+}
+
+int b200_rmsnorm(const void* x, void* residual, const void* weight, float eps, void* out,
+                 int32_t num_tokens, int32_t hidden, void* stream) {
+    if (num_tokens < 0 || hidden <= 0) return B200_ERR_RANGE;
+    if (num_tokens == 0) return B200_OK;
+    if (!x || !weight || !out) return B200_ERR_NULL;
+    if (hidden % 8 != 0 || hidden > 16384) return B200_ERR_SHAPE;
+    if (!aligned16(x) || !aligned16(weight) || !aligned16(out) || (residual && !aligned16(residual))) return B200_ERR_ALIGN;
+    return launch_rmsnorm(x, residual, weight, eps, out, num_tokens, hidden, (cudaStream_t)stream);
+}
+
+int b200_silu_and_mul(const void* x, void* out, int32_t num_tokens, int32_t inter, void* stream) {
+    if (num_tokens < 0 || inter <= 0) return B200_ERR_RANGE;
+    if (num_tokens == 0) return B200_OK;
+    if (!x || !out) return B200_ERR_NULL;
+    if (inter % 8 != 0) return B200_ERR_SHAPE;
+    if (!aligned16(x) || !aligned16(out)) return B200_ERR_ALIGN;
+    return launch_silu_and_mul(x, out, num_tokens, inter, (cudaStream_t)stream);
+}
+
+}  // extern "C"

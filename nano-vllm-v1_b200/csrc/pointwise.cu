@@ -1,0 +1,275 @@
+// HBM-bound byte movers of the path: KV scatter (piece 1), fused per-head RMSNorm+RoPE
+// (piece 4a), hidden-size (add+)RMSNorm (4a'), SiluAndMul (4b).  All use 16-byte coalesced
+// accesses; none is reshaped into a GEMM.
+#include "common.cuh"
+#include "launch.h"
+
+namespace b200 {
+
+// ------------------------------------------------------------------------------------------
+// (1) KV scatter.  One thread moves one 16-byte chunk of K and the matching chunk of V.
+//     Consecutive threads walk consecutive chunks of one token row => every warp issues
+//     full 512-byte coalesced loads and stores.  Reference: attention.py:74-90.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) kv_scatter_kernel(
+    const uint8_t* __restrict__ key, const uint8_t* __restrict__ value,
+    int64_t key_row_bytes, int64_t value_row_bytes,
+    uint8_t* __restrict__ k_cache, uint8_t* __restrict__ v_cache,
+    const int32_t* __restrict__ slot_mapping, int64_t total_chunks, int32_t chunks_per_row_log2) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_chunks; i += stride) {
+        const int64_t tok = i >> chunks_per_row_log2;
+        const int64_t c = i & ((1 << chunks_per_row_log2) - 1);
+        const int32_t slot = __ldg(slot_mapping + tok);
+        if (slot < 0) continue;                                           // attention.py:79-80
+        const int4 kv = ld_nc_v4(key + tok * key_row_bytes + c * 16);
+        const int4 vv = ld_nc_v4(value + tok * value_row_bytes + c * 16);
+        const int64_t dst = (((int64_t)slot) << (chunks_per_row_log2 + 4)) + c * 16;   // 64-bit: SURVEY 7.3(9)
+        st_v4(k_cache + dst, kv);
+        st_v4(v_cache + dst, vv);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// (4a) q_norm/k_norm + RoPE.  One warp per (token, head) row of 128 bf16.
+//      Lane l owns elements {2l, 2l+1} of the low half and {64+2l, 65+2l} of the high half,
+//      i.e. both members of two NeoX rotation pairs => no cross-lane traffic for the rotation,
+//      one butterfly for the sum of squares.  Roundings follow layernorm.py:85-93 and
+//      rotary_embedding.py:60-65 exactly: bf16(x*rstd), bf16(.*w), fp32 rotate, bf16.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) qk_norm_rope_kernel(
+    const __nv_bfloat16* __restrict__ q, int64_t q_token_stride,
+    const __nv_bfloat16* __restrict__ k, int64_t k_token_stride,
+    const int64_t* __restrict__ positions, const float* __restrict__ cos_sin,
+    const __nv_bfloat16* __restrict__ q_weight, const __nv_bfloat16* __restrict__ k_weight, float eps,
+    __nv_bfloat16* __restrict__ q_out, __nv_bfloat16* __restrict__ k_out,
+    int64_t total_rows, int32_t Hq, int32_t Hkv) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (row >= total_rows) return;
+    const int32_t H = Hq + Hkv;
+    const int64_t tok = row / H;
+    const int32_t h = (int32_t)(row - tok * H);
+    const bool is_q = h < Hq;
+    const __nv_bfloat16* src = is_q ? q + tok * q_token_stride + (int64_t)h * B200_HD
+                                    : k + tok * k_token_stride + (int64_t)(h - Hq) * B200_HD;
+    __nv_bfloat16* dst = is_q ? q_out + (tok * Hq + h) * B200_HD : k_out + (tok * Hkv + (h - Hq)) * B200_HD;
+    const __nv_bfloat16* w = is_q ? q_weight : k_weight;
+
+    const float2 lo = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(src + 2 * lane));
+    const float2 hi = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(src + 64 + 2 * lane));
+    float ss = lo.x * lo.x + lo.y * lo.y + hi.x * hi.x + hi.y * hi.y;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    const float rstd = rsqrtf(__fadd_rn(ss * (1.0f / B200_HD), eps));
+    // weight == nullptr => rotation only (stand-alone RotaryEmbedding.forward)
+    const float2 wlo = w ? unpack_bf16x2(*reinterpret_cast<const uint32_t*>(w + 2 * lane)) : make_float2(1.f, 1.f);
+    const float2 whi = w ? unpack_bf16x2(*reinterpret_cast<const uint32_t*>(w + 64 + 2 * lane)) : make_float2(1.f, 1.f);
+    // bf16(x * rstd) then bf16(that * w): two roundings, as in the reference
+    auto nrm = [&](float x, float wt) {
+        if (w == nullptr) return x;
+        const float y = __bfloat162float(__float2bfloat16_rn(__fmul_rn(x, rstd)));
+        return __bfloat162float(__float2bfloat16_rn(__fmul_rn(y, wt)));
+    };
+    const float x1a = nrm(lo.x, wlo.x), x1b = nrm(lo.y, wlo.y);
+    const float x2a = nrm(hi.x, whi.x), x2b = nrm(hi.y, whi.y);
+    const float* cs = cos_sin + positions[tok] * B200_HD;                 // [cos(64) | sin(64)]
+    const float2 c = *reinterpret_cast<const float2*>(cs + 2 * lane);
+    const float2 s = *reinterpret_cast<const float2*>(cs + 64 + 2 * lane);
+    // y1 = x1*cos - x2*sin ; y2 = x2*cos + x1*sin  (un-fused, matching eager fp32)
+    const float y1a = __fsub_rn(__fmul_rn(x1a, c.x), __fmul_rn(x2a, s.x));
+    const float y1b = __fsub_rn(__fmul_rn(x1b, c.y), __fmul_rn(x2b, s.y));
+    const float y2a = __fadd_rn(__fmul_rn(x2a, c.x), __fmul_rn(x1a, s.x));
+    const float y2b = __fadd_rn(__fmul_rn(x2b, c.y), __fmul_rn(x1b, s.y));
+    *reinterpret_cast<uint32_t*>(dst + 2 * lane) = pack_bf16x2(y1a, y1b);
+    *reinterpret_cast<uint32_t*>(dst + 64 + 2 * lane) = pack_bf16x2(y2a, y2b);
+}
+
+// ------------------------------------------------------------------------------------------
+// (4a') hidden-size RMSNorm with optional residual add.  One CTA per token, 16-byte loads,
+//       values stay in registers between the reduction and the scaling pass.
+// ------------------------------------------------------------------------------------------
+template <int MAX_CHUNKS>
+__global__ void __launch_bounds__(256) rmsnorm_kernel(
+    const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ residual,
+    const __nv_bfloat16* __restrict__ weight, float eps, __nv_bfloat16* __restrict__ out, int32_t hidden) {
+    __shared__ float red[8];
+    const int64_t base = (int64_t)blockIdx.x * hidden;
+    const int nchunks = hidden >> 3;
+    float v[MAX_CHUNKS][8];
+    float ss = 0.f;
+#pragma unroll
+    for (int it = 0; it < MAX_CHUNKS; ++it) {
+        const int c = threadIdx.x + it * 256;
+        if (c < nchunks) {
+            const int4 xi = *reinterpret_cast<const int4*>(x + base + c * 8);
+            const uint32_t xs[4] = {(uint32_t)xi.x, (uint32_t)xi.y, (uint32_t)xi.z, (uint32_t)xi.w};
+            if (residual != nullptr) {
+                const int4 ri = *reinterpret_cast<const int4*>(residual + base + c * 8);
+                const uint32_t rs[4] = {(uint32_t)ri.x, (uint32_t)ri.y, (uint32_t)ri.z, (uint32_t)ri.w};
+                uint32_t ro[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float2 a = unpack_bf16x2(xs[j]), b = unpack_bf16x2(rs[j]);
+                    v[it][2 * j] = __fadd_rn(a.x, b.x);
+                    v[it][2 * j + 1] = __fadd_rn(a.y, b.y);
+                    ro[j] = pack_bf16x2(v[it][2 * j], v[it][2 * j + 1]);
+                }
+                *reinterpret_cast<int4*>(residual + base + c * 8) = make_int4(ro[0], ro[1], ro[2], ro[3]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float2 a = unpack_bf16x2(xs[j]);
+                    v[it][2 * j] = a.x;
+                    v[it][2 * j + 1] = a.y;
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) ss += v[it][j] * v[it][j];
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    float tot = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) tot += red[i];
+    const float rstd = rsqrtf(__fadd_rn(tot / (float)hidden, eps));
+#pragma unroll
+    for (int it = 0; it < MAX_CHUNKS; ++it) {
+        const int c = threadIdx.x + it * 256;
+        if (c < nchunks) {
+            const int4 wi = *reinterpret_cast<const int4*>(weight + c * 8);
+            const uint32_t ws[4] = {(uint32_t)wi.x, (uint32_t)wi.y, (uint32_t)wi.z, (uint32_t)wi.w};
+            uint32_t o[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 w2 = unpack_bf16x2(ws[j]);
+                const float a = __bfloat162float(__float2bfloat16_rn(__fmul_rn(v[it][2 * j], rstd)));
+                const float b = __bfloat162float(__float2bfloat16_rn(__fmul_rn(v[it][2 * j + 1], rstd)));
+                o[j] = pack_bf16x2(__fmul_rn(a, w2.x), __fmul_rn(b, w2.y));
+            }
+            *reinterpret_cast<int4*>(out + base + c * 8) = make_int4(o[0], o[1], o[2], o[3]);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// (4b) SiluAndMul: out[t, i] = silu(x[t, i]) * x[t, I + i], fp32, one rounding.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) silu_and_mul_kernel(
+    const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, int64_t total_chunks, int32_t chunks_per_row) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_chunks; i += stride) {
+        const int64_t t = i / chunks_per_row;
+        const int64_t c = i - t * chunks_per_row;
+        const __nv_bfloat16* row = x + t * (int64_t)chunks_per_row * 16;
+        const int4 gi = ld_nc_v4(row + c * 8);
+        const int4 ui = ld_nc_v4(row + (int64_t)chunks_per_row * 8 + c * 8);
+        const uint32_t gs[4] = {(uint32_t)gi.x, (uint32_t)gi.y, (uint32_t)gi.z, (uint32_t)gi.w};
+        const uint32_t us[4] = {(uint32_t)ui.x, (uint32_t)ui.y, (uint32_t)ui.z, (uint32_t)ui.w};
+        uint32_t o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float2 g = unpack_bf16x2(gs[j]), u = unpack_bf16x2(us[j]);
+            const float a = __fdividef(g.x, 1.0f + __expf(-g.x)) * u.x;
+            const float b = __fdividef(g.y, 1.0f + __expf(-g.y)) * u.y;
+            o[j] = pack_bf16x2(a, b);
+        }
+        st_na_v4(out + i * 8, make_int4(o[0], o[1], o[2], o[3]));
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// host launchers
+// ------------------------------------------------------------------------------------------
+static inline int grid_for(int64_t threads_needed, int block, int waves_cap = 8) {
+    int64_t blocks = (threads_needed + block - 1) / block;
+    const int64_t cap = (int64_t)sm_count() * waves_cap;       // multiples of the SM count; grid-stride beyond
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return (int)blocks;
+}
+
+int launch_kv_scatter(const void* key, const void* value, int64_t key_row_stride, int64_t value_row_stride,
+                      void* k_cache, void* v_cache, const int32_t* slot_mapping,
+                      int32_t T, int32_t Hkv, int32_t D, cudaStream_t stream) {
+    const int32_t row_bytes = Hkv * D * 2;
+    const int32_t chunks = row_bytes / 16;
+    int lg = 0;
+    while ((1 << lg) < chunks) ++lg;
+    if ((1 << lg) != chunks) {
+        // non power-of-two rows (e.g. 5 heads): fall back to one "row" per head
+        return launch_kv_scatter_generic(key, value, key_row_stride, value_row_stride, k_cache, v_cache,
+                                         slot_mapping, T, Hkv, D, stream);
+    }
+    const int64_t total = (int64_t)T * chunks;
+    kv_scatter_kernel<<<grid_for(total, 256), 256, 0, stream>>>(
+        (const uint8_t*)key, (const uint8_t*)value, key_row_stride * 2, value_row_stride * 2,
+        (uint8_t*)k_cache, (uint8_t*)v_cache, slot_mapping, total, lg);
+    return (int)cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) kv_scatter_generic_kernel(
+    const uint8_t* __restrict__ key, const uint8_t* __restrict__ value, int64_t key_row_bytes, int64_t value_row_bytes,
+    uint8_t* __restrict__ k_cache, uint8_t* __restrict__ v_cache, const int32_t* __restrict__ slot_mapping,
+    int64_t total_chunks, int32_t chunks_per_row) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_chunks; i += stride) {
+        const int64_t tok = i / chunks_per_row;
+        const int64_t c = i - tok * chunks_per_row;
+        const int32_t slot = __ldg(slot_mapping + tok);
+        if (slot < 0) continue;
+        const int4 kv = ld_nc_v4(key + tok * key_row_bytes + c * 16);
+        const int4 vv = ld_nc_v4(value + tok * value_row_bytes + c * 16);
+        const int64_t dst = ((int64_t)slot * chunks_per_row + c) * 16;
+        st_v4(k_cache + dst, kv);
+        st_v4(v_cache + dst, vv);
+    }
+}
+
+int launch_kv_scatter_generic(const void* key, const void* value, int64_t key_row_stride, int64_t value_row_stride,
+                              void* k_cache, void* v_cache, const int32_t* slot_mapping,
+                              int32_t T, int32_t Hkv, int32_t D, cudaStream_t stream) {
+    const int32_t chunks = Hkv * D * 2 / 16;
+    const int64_t total = (int64_t)T * chunks;
+    kv_scatter_generic_kernel<<<grid_for(total, 256), 256, 0, stream>>>(
+        (const uint8_t*)key, (const uint8_t*)value, key_row_stride * 2, value_row_stride * 2,
+        (uint8_t*)k_cache, (uint8_t*)v_cache, slot_mapping, total, chunks);
+    return (int)cudaGetLastError();
+}
+
+int launch_qk_norm_rope(const void* q, int64_t q_token_stride, const void* k, int64_t k_token_stride,
+                        const int64_t* positions, const float* cos_sin, const void* qw, const void* kw, float eps,
+                        void* q_out, void* k_out, int32_t T, int32_t Hq, int32_t Hkv, cudaStream_t stream) {
+    const int64_t rows = (int64_t)T * (Hq + Hkv);
+    const int64_t blocks = (rows + 7) / 8;
+    qk_norm_rope_kernel<<<(unsigned)blocks, 256, 0, stream>>>(
+        (const __nv_bfloat16*)q, q_token_stride, (const __nv_bfloat16*)k, k_token_stride, positions, cos_sin,
+        (const __nv_bfloat16*)qw, (const __nv_bfloat16*)kw, eps, (__nv_bfloat16*)q_out, (__nv_bfloat16*)k_out,
+        rows, Hq, Hkv);
+    return (int)cudaGetLastError();
+}
+
+int launch_rmsnorm(const void* x, void* residual, const void* weight, float eps, void* out,
+                   int32_t T, int32_t hidden, cudaStream_t stream) {
+    const int chunks = hidden / 8;
+    if (chunks <= 256 * 2)
+        rmsnorm_kernel<2><<<T, 256, 0, stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)residual,
+                                                 (const __nv_bfloat16*)weight, eps, (__nv_bfloat16*)out, hidden);
+    else
+        rmsnorm_kernel<8><<<T, 256, 0, stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)residual,
+                                                 (const __nv_bfloat16*)weight, eps, (__nv_bfloat16*)out, hidden);
+    return (int)cudaGetLastError();
+}
+
+int launch_silu_and_mul(const void* x, void* out, int32_t T, int32_t inter, cudaStream_t stream) {
+    const int32_t chunks_per_row = inter / 8;
+    const int64_t total = (int64_t)T * chunks_per_row;
+    silu_and_mul_kernel<<<grid_for(total, 256, 16), 256, 0, stream>>>(
+        (const __nv_bfloat16*)x, (__nv_bfloat16*)out, total, chunks_per_row);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace b200

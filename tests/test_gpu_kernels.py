@@ -1,0 +1,321 @@
+"""GPU parity tests (-m gpu): every kernel, called through the C ABI (b200attn.ops ->
+libb200attn.so), against the CPU oracle on identical seeded inputs.
+
+Bars: KV scatter bit-exact; attention max-abs <= 2e-2 (BASELINE.json north_star); pointwise
+<= 1 bf16 ulp of the oracle (the reference's own compiled form is only defined to that)."""
+import glob
+import os
+
+import pytest
+import torch
+
+import oracle
+from helpers import GOLDEN, bf16_ulp, make_paged_case, scatter_inputs
+
+pytestmark = pytest.mark.gpu
+ATOL = 2e-2
+SCALE = 128 ** -0.5
+
+
+@pytest.fixture(scope="module")
+def ops():
+    assert torch.cuda.is_available()
+    import b200attn
+    b200attn.load_library()
+    return b200attn.ops
+
+
+def dev(t):
+    return t.cuda() if isinstance(t, torch.Tensor) else t
+
+
+def maxerr(a, b):
+    return (a.float().cpu() - b.float().cpu()).abs().max().item()
+
+
+# ---------------------------------------------------------------------------- scatter
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "scatter_*.pt"))))
+def test_scatter_matches_reference_golden(ops, path):
+    meta = torch.load(path)
+    qkv, k, v, kc, vc = scatter_inputs(meta)
+    Hq, Hkv, D, T = meta["Hq"], meta["Hkv"], meta["D"], meta["T"]
+    qkv_d = qkv.cuda()
+    v_d = qkv_d[:, (Hq + Hkv) * D:].view(T, Hkv, D)              # strided view, like the reference
+    kc_d, vc_d = kc.cuda(), vc.cuda()
+    ops.store_kvcache(k.cuda(), v_d, kc_d, vc_d, meta["slot_mapping"].cuda())
+    row = Hkv * D
+    assert torch.equal(kc_d.cpu().view(-1, row)[meta["touched"]], meta["k_rows"])
+    assert torch.equal(vc_d.cpu().view(-1, row)[meta["touched"]], meta["v_rows"])
+    oracle.kv_scatter(k, v, kc, vc, meta["slot_mapping"])
+    assert torch.equal(kc_d.cpu(), kc) and torch.equal(vc_d.cpu(), vc)
+
+
+@pytest.mark.parametrize("Hkv", [8, 4, 2, 1, 5])
+def test_scatter_random_bit_exact(ops, Hkv):
+    g = torch.Generator().manual_seed(Hkv)
+    T, D, nb, Hq = 3000, 128, 20, 2 * Hkv
+    qkv = torch.randn(T, (Hq + 2 * Hkv) * D, generator=g).bfloat16()
+    k = qkv[:, Hq * D:(Hq + Hkv) * D].reshape(T, Hkv, D).contiguous()
+    slots = torch.randperm(nb * 256, generator=g)[:T].to(torch.int32)
+    slots[torch.rand(T, generator=g) < 0.1] = -1
+    kc = torch.randn(nb, 256, Hkv, D, generator=g).bfloat16()
+    vc = torch.randn(nb, 256, Hkv, D, generator=g).bfloat16()
+    qkv_d = qkv.cuda()
+    kc_d, vc_d = kc.cuda(), vc.cuda()
+    ops.store_kvcache(k.cuda(), qkv_d[:, (Hq + Hkv) * D:].view(T, Hkv, D), kc_d, vc_d, slots.cuda())
+    oracle.kv_scatter(k, qkv[:, (Hq + Hkv) * D:].view(T, Hkv, D), kc, vc, slots)
+    assert torch.equal(kc_d.cpu(), kc) and torch.equal(vc_d.cpu(), vc)
+
+
+def test_scatter_empty_and_all_padding(ops):
+    kc = torch.zeros(1, 256, 2, 128, dtype=torch.bfloat16, device="cuda")
+    vc = torch.zeros_like(kc)
+    e = torch.zeros(0, 2, 128, dtype=torch.bfloat16, device="cuda")
+    ops.store_kvcache(e, e, kc, vc, torch.zeros(0, dtype=torch.int32, device="cuda"))
+    k = torch.ones(5, 2, 128, dtype=torch.bfloat16, device="cuda")
+    ops.store_kvcache(k, k, kc, vc, torch.full((5,), -1, dtype=torch.int32, device="cuda"))
+    assert kc.abs().sum().item() == 0 and vc.abs().sum().item() == 0
+
+
+# ---------------------------------------------------------------------------- decode
+RAGGED = [1, 15, 16, 17, 255, 256, 257, 0, 511, 1024, 1300, 33]
+
+
+@pytest.mark.parametrize("Hq,Hkv", [(32, 8), (16, 4), (8, 2), (4, 1), (16, 8), (5, 1), (8, 1), (40, 8), (16, 1)])
+@pytest.mark.parametrize("splits", [None, 1, 3, 8])
+def test_decode_ragged_vs_oracle(ops, Hq, Hkv, splits):
+    c = make_paged_case(100 + Hq, [1] * len(RAGGED), RAGGED, Hq, Hkv, pad=0, table_width=8)
+    want = oracle.attn_decode(c["q"], c["k_cache"], c["v_cache"], c["context_lens"], c["block_tables"], SCALE)
+    got = ops.attn_decode(dev(c["q"]), dev(c["k_cache"]), dev(c["v_cache"]), dev(c["context_lens"]),
+                          dev(c["block_tables"]), SCALE, num_splits=splits)
+    assert maxerr(got, want) <= ATOL
+    assert got.cpu()[RAGGED.index(0)].abs().sum() == 0            # graph padding row -> zeros
+
+
+def test_decode_minus_one_padding_and_nan_garbage_beyond_context(ops):
+    """Eager tables are padded with -1 and the cache tail holds whatever torch.empty left:
+    neither may leak into the result."""
+    lens = [300, 5, 256]
+    c = make_paged_case(9, [1] * 3, lens, 8, 2, pad=-1, table_width=4)
+    kc, vc = c["k_cache"].clone(), c["v_cache"].clone()
+    for b, L in enumerate(lens):                                   # poison every row past the context
+        nblk = (L + 255) // 256
+        last = int(c["block_tables"][b, nblk - 1])
+        if L % 256:
+            kc[last, L % 256:] = float("nan")
+            vc[last, L % 256:] = float("nan")
+    want = oracle.attn_decode(c["q"], c["k_cache"], c["v_cache"], c["context_lens"], c["block_tables"], SCALE)
+    got = ops.attn_decode(dev(c["q"]), dev(kc), dev(vc), dev(c["context_lens"]), dev(c["block_tables"]), SCALE)
+    assert torch.isfinite(got.float()).all()
+    assert maxerr(got, want) <= ATOL
+
+
+def test_decode_cuda_graph_replay_with_changing_lengths(ops):
+    """model_runner.py:640-715 semantics: capture with zero lengths/tables, replay with real ones."""
+    Hq, Hkv, B = 16, 8, 8
+    c = make_paged_case(21, [1] * B, [700, 3, 0, 256, 90, 0, 1000, 511], Hq, Hkv, pad=0, table_width=6)
+    q = torch.zeros(B, Hq, 128, dtype=torch.bfloat16, device="cuda")
+    lens = torch.zeros(B, dtype=torch.int32, device="cuda")
+    bt = torch.zeros(B, 6, dtype=torch.int32, device="cuda")
+    kc, vc = dev(c["k_cache"]), dev(c["v_cache"])
+    out = torch.zeros_like(q)
+    ops.reserve_decode_workspace(B, Hq, Hkv, 6 * 256, q.device)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        ops.attn_decode(q, kc, vc, lens, bt, SCALE, out=out)
+    torch.cuda.current_stream().wait_stream(s)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        ops.attn_decode(q, kc, vc, lens, bt, SCALE, out=out)
+    q.copy_(c["q"]); lens.copy_(c["context_lens"]); bt.copy_(c["block_tables"])
+    g.replay()
+    want = oracle.attn_decode(c["q"], c["k_cache"], c["v_cache"], c["context_lens"], c["block_tables"], SCALE)
+    assert maxerr(out, want) <= ATOL
+
+
+def test_decode_full_size_cfg3_properties(ops):
+    """BASELINE configs[2] at full size (512 seqs x 4096 ctx, 32q/8kv): (a) a random subset of
+    sequences against the oracle, (b) V == const => output == const (softmax weights sum to 1),
+    (c) split-K result == unsplit result."""
+    B, L, Hq, Hkv, D = 512, 4096, 32, 8, 128
+    nblk = B * (L // 256)
+    g = torch.Generator(device="cuda").manual_seed(0)
+    kc = torch.randn(nblk, 256, Hkv, D, generator=g, device="cuda", dtype=torch.bfloat16)
+    vc = torch.randn(nblk, 256, Hkv, D, generator=g, device="cuda", dtype=torch.bfloat16)
+    q = torch.randn(B, Hq, D, generator=g, device="cuda", dtype=torch.bfloat16)
+    perm = torch.randperm(nblk, generator=torch.Generator().manual_seed(1)).to(torch.int32)
+    bt = perm.view(B, L // 256).cuda()
+    lens = torch.full((B,), L, dtype=torch.int32, device="cuda")
+    out1 = ops.attn_decode(q, kc, vc, lens, bt, SCALE, num_splits=1)
+    out4 = ops.attn_decode(q, kc, vc, lens, bt, SCALE, num_splits=4)
+    assert maxerr(out1, out4) <= 4e-3
+    idx = torch.tensor([0, 17, 255, 511])
+    sub_blocks = bt[idx.cuda()].cpu()
+    uniq, inv = torch.unique(sub_blocks, return_inverse=True)
+    want = oracle.attn_decode(q[idx.cuda()].cpu(), kc[uniq.cuda().long()].cpu(), vc[uniq.cuda().long()].cpu(),
+                              lens[idx.cuda()].cpu(), inv.to(torch.int32), SCALE)
+    assert maxerr(out1[idx.cuda()], want) <= ATOL
+    const = torch.randn(Hkv, D, generator=torch.Generator().manual_seed(2)).bfloat16().cuda()
+    vc.copy_(const.view(1, 1, Hkv, D).expand_as(vc))
+    outc = ops.attn_decode(q, kc, vc, lens, bt, SCALE)
+    expect = const.repeat_interleave(Hq // Hkv, dim=0).unsqueeze(0).expand(B, Hq, D)
+    assert maxerr(outc, expect) <= 2 ** -7 * const.abs().max().item() + 1e-6
+
+
+# ---------------------------------------------------------------------------- prefill
+@pytest.mark.parametrize("variant", [1])
+@pytest.mark.parametrize("Hq,Hkv", [(16, 8), (4, 1), (5, 1), (8, 2)])
+def test_prefill_unpaged_vs_oracle(ops, Hq, Hkv, variant):
+    """Sub-paths A/B: Lq == Lk, fresh k (contiguous) and v (strided view of qkv)."""
+    lens = [128, 1, 63, 64, 65, 300, 7]
+    g = torch.Generator().manual_seed(5)
+    T, D = sum(lens), 128
+    qkv = torch.randn(T, (Hq + 2 * Hkv) * D, generator=g).bfloat16()
+    q = qkv[:, :Hq * D].reshape(T, Hq, D).contiguous()
+    k = qkv[:, Hq * D:(Hq + Hkv) * D].reshape(T, Hkv, D).contiguous()
+    v = qkv[:, (Hq + Hkv) * D:].view(T, Hkv, D)
+    cu = torch.tensor([0] + torch.tensor(lens).cumsum(0).tolist(), dtype=torch.int32)
+    want = oracle.attn_varlen(q, k, v, cu, cu, SCALE)
+    qkv_d = qkv.cuda()
+    got = ops.attn_varlen(q.cuda(), k.cuda(), qkv_d[:, (Hq + Hkv) * D:].view(T, Hkv, D), cu.cuda(), cu.cuda(),
+                          max(lens), max(lens), SCALE, variant=variant)
+    assert maxerr(got, want) <= ATOL
+
+
+@pytest.mark.parametrize("variant", [1])
+@pytest.mark.parametrize("Hq,Hkv", [(16, 8), (4, 1), (5, 1), (32, 8)])
+def test_prefill_paged_chunked_mixed_vs_oracle(ops, Hq, Hkv, variant):
+    """Sub-path C: chunked prefill, prefix hits, decode rows mixed with prefill rows, -1 padding."""
+    lens_k = [700, 129, 128, 1, 257, 513, 64, 1000]
+    lens_q = [188, 1, 128, 1, 1, 257, 64, 40]
+    c = make_paged_case(31 + Hq, lens_q, lens_k, Hq, Hkv, pad=-1)
+    want = oracle.attn_varlen(c["q"], c["k_cache"], c["v_cache"], c["cu_seqlens_q"], c["cu_seqlens_k"], SCALE,
+                              c["block_tables"])
+    got = ops.attn_varlen(dev(c["q"]), dev(c["k_cache"]), dev(c["v_cache"]), dev(c["cu_seqlens_q"]),
+                          dev(c["cu_seqlens_k"]), c["max_seqlen_q"], c["max_seqlen_k"], SCALE,
+                          block_table=dev(c["block_tables"]), variant=variant)
+    assert maxerr(got, want) <= ATOL
+
+
+@pytest.mark.parametrize("variant", [1])
+def test_prefill_long_causal_row_sampled_vs_oracle(ops, variant):
+    """One 4,160-token causal sequence (Hq 8 / Hkv 1, the TP=8 shape): full oracle compare."""
+    L = 4160
+    c = make_paged_case(77, [L], [L], 8, 1)
+    want = oracle.attn_varlen(c["q"], c["k_cache"], c["v_cache"], c["cu_seqlens_q"], c["cu_seqlens_k"], SCALE,
+                              c["block_tables"])
+    got = ops.attn_varlen(dev(c["q"]), dev(c["k_cache"]), dev(c["v_cache"]), dev(c["cu_seqlens_q"]),
+                          dev(c["cu_seqlens_k"]), L, L, SCALE, block_table=dev(c["block_tables"]), variant=variant)
+    assert maxerr(got, want) <= ATOL
+
+
+# ---------------------------------------------------------------------------- Attention.forward
+def test_attention_forward_prefix_sharing_same_step(ops):
+    """a branch scheduled in the same step reads prefix blocks that another sequence
+    writes in that very forward pass; the scatter must be ordered before every read."""
+    from b200attn.layers.attention import Attention
+    from b200attn.utils.context import reset_context, set_context
+    Hq, Hkv, D, P = 8, 2, 128, 256
+    g = torch.Generator().manual_seed(3)
+    prefix, tail = 512, 40
+    lens_q = [prefix + tail, tail, tail]                 # seq 0 computes the prefix, 1 and 2 only their tails
+    lens_k = [prefix + tail] * 3
+    T = sum(lens_q)
+    q = torch.randn(T, Hq, D, generator=g).bfloat16()
+    k = torch.randn(T, Hkv, D, generator=g).bfloat16()
+    v = torch.randn(T, Hkv, D, generator=g).bfloat16()
+    bt = torch.tensor([[5, 2, 7], [5, 2, 1], [5, 2, 0]], dtype=torch.int32)   # shared blocks 5, 2
+    slots = []
+    for b in range(3):
+        start = 0 if b == 0 else prefix
+        for pos in range(start, prefix + tail):
+            slots.append(int(bt[b, pos // P]) * P + pos % P)
+    slot_mapping = torch.tensor(slots, dtype=torch.int32)
+    cu_q = torch.tensor([0, lens_q[0], lens_q[0] + tail, T], dtype=torch.int32)
+    cu_k = torch.tensor([0, lens_k[0], 2 * lens_k[0], 3 * lens_k[0]], dtype=torch.int32)
+    ctx = (cu_q, cu_k, max(lens_q), max(lens_k), slot_mapping, torch.tensor(lens_k, dtype=torch.int32), bt, None)
+    kc = torch.full((8, P, Hkv, D), float("nan")).bfloat16()      # stale garbage everywhere
+    vc = kc.clone()
+    attn = Attention(Hq, D, SCALE, Hkv)
+    attn.k_cache, attn.v_cache = kc.cuda(), vc.cuda()
+    set_context(*[dev(t) for t in ctx])
+    got = attn(q.cuda(), k.cuda(), v.cuda())
+    reset_context()
+    want = oracle.attention_forward(q, k, v, kc, vc, oracle.Context(*ctx), SCALE)
+    assert torch.isfinite(got.float()).all()
+    assert maxerr(got, want) <= ATOL
+    written = ~torch.isnan(kc.float()).any(-1).any(-1)
+    assert torch.equal(attn.k_cache.cpu()[written], kc[written])
+
+
+def test_attention_forward_config0_prefill_then_decode(ops):
+    import __graft_entry__ as g
+    g.smoke()
+
+
+def test_attention_eager_decode_routes_to_decode_kernel(ops):
+    """enforce_eager / bs > 512: varlen call with every q_len == 1."""
+    from b200attn.layers.attention import Attention
+    from b200attn.utils.context import reset_context, set_context
+    lens = [5, 300, 256, 1]
+    c = make_paged_case(13, [1] * 4, lens, 16, 8, pad=-1)
+    attn = Attention(16, 128, SCALE, 8)
+    attn.k_cache, attn.v_cache = dev(c["k_cache"]), dev(c["v_cache"])
+    set_context(dev(c["cu_seqlens_q"]), dev(c["cu_seqlens_k"]), 1, max(lens),
+                torch.full((4,), -1, dtype=torch.int32, device="cuda"), dev(c["context_lens"]),
+                dev(c["block_tables"]), None)
+    knew = torch.zeros(4, 8, 128, dtype=torch.bfloat16, device="cuda")
+    got = attn(dev(c["q"]), knew, knew)
+    reset_context()
+    want = oracle.attn_varlen(c["q"], c["k_cache"], c["v_cache"], c["cu_seqlens_q"], c["cu_seqlens_k"], SCALE,
+                              c["block_tables"])
+    assert maxerr(got, want) <= ATOL
+
+
+# ---------------------------------------------------------------------------- pointwise
+def _ulp_ok(got, want, n=1):
+    got, want = got.float().cpu(), want.float()
+    return ((got - want).abs() <= n * bf16_ulp(want) + 1e-30).all().item()
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "pointwise_*.pt"))))
+def test_pointwise_vs_reference_golden(ops, path):
+    m = torch.load(path)
+    T, Hq, Hkv, D = m["T"], m["Hq"], m["Hkv"], m["D"]
+    qkv = m["qkv"].cuda()
+    q, k, _ = qkv.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
+    cache = oracle.make_cos_sin_cache(D, m["max_pos"], m["base"]).view(-1, D).cuda()
+    qo, ko = ops.qk_norm_rope(q.view(T, Hq, D), k.view(T, Hkv, D), m["positions"].cuda(), m["q_weight"].cuda(),
+                              m["k_weight"].cuda(), cache, m["eps"])
+    assert _ulp_ok(qo, m["q_out"]) and _ulp_ok(ko, m["k_out"])
+    assert (qo.cpu() == m["q_out"]).float().mean() > 0.995       # almost always identical bits
+    act = ops.silu_and_mul(m["act_in"].cuda())
+    assert _ulp_ok(act, oracle.silu_and_mul(m["act_in"], "compiled"))
+    assert _ulp_ok(act, m["act_out_eager"], 2)
+    y = ops.rms_norm(m["h"].cuda(), m["h_weight"].cuda(), m["eps"])
+    assert _ulp_ok(y, m["h_norm"])
+    r = m["r"].clone().cuda()
+    y2, r2 = ops.rms_norm(m["h"].cuda(), m["h_weight"].cuda(), m["eps"], r)
+    assert _ulp_ok(y2, m["hr_norm"]) and torch.equal(r2.cpu(), m["hr_res"])
+
+
+def test_rotation_only_and_large_shapes(ops):
+    g = torch.Generator().manual_seed(8)
+    T, Hq, Hkv, D = 1000, 32, 8, 128
+    qkv = torch.randn(T, (Hq + 2 * Hkv) * D, generator=g).bfloat16()
+    q, k, _ = qkv.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
+    q, k = q.view(T, Hq, D), k.view(T, Hkv, D)
+    pos = torch.randint(0, 40960, (T,), generator=g)
+    cache = oracle.make_cos_sin_cache(D, 40960, 1e6)
+    cos, sin = cache[pos].chunk(2, dim=-1)
+    wq, wk = oracle.rope(q, cos, sin), oracle.rope(k, cos, sin)
+    qkv_d = qkv.cuda()
+    qd, kd, _ = qkv_d.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
+    gq, gk = ops.qk_norm_rope(qd.view(T, Hq, D), kd.view(T, Hkv, D), pos.cuda(), None, None, cache.view(-1, D).cuda())
+    assert _ulp_ok(gq, wq) and _ulp_ok(gk, wk)
+    x = (3 * torch.randn(777, 2 * 12288, generator=g)).bfloat16()
+    assert _ulp_ok(ops.silu_and_mul(x.cuda()), oracle.silu_and_mul(x))
+    h = torch.randn(300, 5120, generator=g).bfloat16()
+    w = (1 + 0.1 * torch.randn(5120, generator=g)).bfloat16()
+    assert _ulp_ok(ops.rms_norm(h.cuda(), w.cuda(), 1e-6), oracle.rms_norm(h, w))
