@@ -151,6 +151,10 @@ int b200_attn_prefill(const void* q, int64_t q_token_stride, const void* k, cons
         if (!prefill_tc_available()) return B200_ERR_UNAVAILABLE;
         return launch_attn_prefill_tc(a, (cudaStream_t)stream);
     }
+    if (variant == 3) {
+        if (!prefill_tc_available()) return B200_ERR_UNAVAILABLE;
+        return launch_attn_prefill_tc1(a, (cudaStream_t)stream);
+    }
     if (variant != 1) return B200_ERR_RANGE;
     return launch_attn_prefill_mma(a, (cudaStream_t)stream);
 }

@@ -42,7 +42,8 @@ struct PrefillArgs {
     int32_t batch, total_q, max_q, max_k, Hq, Hkv; int64_t num_cache_blocks; float scale;
 };
 int launch_attn_prefill_mma(const PrefillArgs& a, cudaStream_t stream);
-int launch_attn_prefill_tc(const PrefillArgs& a, cudaStream_t stream);   // tcgen05/TMEM/TMA
+int launch_attn_prefill_tc(const PrefillArgs& a, cudaStream_t stream);   // tcgen05/TMEM/TMA, 2 query tiles in flight
+int launch_attn_prefill_tc1(const PrefillArgs& a, cudaStream_t stream);  // same, 1 query tile (bring-up / small shapes)
 bool prefill_tc_available();
 
 }  // namespace b200
