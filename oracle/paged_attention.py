@@ -17,12 +17,15 @@ CPU fp32 restatement of what the reference's `Attention.forward`
     aligned to the BOTTOM-RIGHT corner (query i sees keys j <= i + Lk - Lq); a row with no
     visible key yields 0; softmax in fp32 on scale * q.k.
 
-Parity status: flash-attn has no CPU code path, so this file cannot be checked against
-the reference in the build container ("parity unpinned" here); it is pinned on the GPU
-box against flash-attn's own entry points, called exactly as attention.py:229-232 and
-:242-248 call them -- live in tests/test_gpu_vs_flashattn.py and through the committed
-fixtures tests/golden/attn_fa2_*.pt (generated there by tools/make_golden_gpu.py).
-Independently, tests/test_oracle_cpu.py checks it against dense softmax(QK^T)V.
+Parity status: PINNED.  flash-attn has no CPU code path, so the reference cannot run in the
+build container; instead the unmodified reference `Attention.forward` was run on a B200
+(tools/make_golden_gpu.py, reference installed offline under baseline/_ref) on seeded cases
+covering unpaged prefill, paged chunked/mixed prefill (G = 2, 4, 5) and graph-form decode with
+padding rows; the outputs are committed as tests/golden/attn_ref_*.pt and
+tests/test_oracle_cpu.py::test_attention_oracle_matches_reference_forward_on_gpu holds this file
+to them (max-abs <= 2e-2, cache after the step bit-exact by SHA-256).
+tests/test_gpu_vs_flashattn.py re-checks live against flash-attn's entry points on the box, and
+tests/test_oracle_cpu.py also checks first principles (dense softmax(QK^T)V).
 """
 from typing import Optional
 

@@ -10,10 +10,13 @@ import pytest
 import torch
 
 import oracle
-from helpers import GOLDEN, bf16_ulp, make_paged_case, scatter_inputs
+from helpers import GOLDEN, bf16_ulp, make_forward_case, make_paged_case, scatter_inputs, tensor_sha256
 
 pytestmark = pytest.mark.gpu
 ATOL = 2e-2
+# prefill kernel variants of b200_attn_prefill: 0 = what the drop-in uses (auto), 1 = mma.sync,
+# 2 = tcgen05 two query tiles in flight, 3 = tcgen05 one tile
+VARIANTS = [0, 1, 2, 3]
 SCALE = 128 ** -0.5
 
 
@@ -164,7 +167,7 @@ def test_decode_full_size_cfg3_properties(ops):
 
 
 # ---------------------------------------------------------------------------- prefill
-@pytest.mark.parametrize("variant", [1])
+@pytest.mark.parametrize("variant", VARIANTS)
 @pytest.mark.parametrize("Hq,Hkv", [(16, 8), (4, 1), (5, 1), (8, 2)])
 def test_prefill_unpaged_vs_oracle(ops, Hq, Hkv, variant):
     """Sub-paths A/B: Lq == Lk, fresh k (contiguous) and v (strided view of qkv)."""
@@ -183,7 +186,7 @@ def test_prefill_unpaged_vs_oracle(ops, Hq, Hkv, variant):
     assert maxerr(got, want) <= ATOL
 
 
-@pytest.mark.parametrize("variant", [1])
+@pytest.mark.parametrize("variant", VARIANTS)
 @pytest.mark.parametrize("Hq,Hkv", [(16, 8), (4, 1), (5, 1), (32, 8)])
 def test_prefill_paged_chunked_mixed_vs_oracle(ops, Hq, Hkv, variant):
     """Sub-path C: chunked prefill, prefix hits, decode rows mixed with prefill rows, -1 padding."""
@@ -198,7 +201,7 @@ def test_prefill_paged_chunked_mixed_vs_oracle(ops, Hq, Hkv, variant):
     assert maxerr(got, want) <= ATOL
 
 
-@pytest.mark.parametrize("variant", [1])
+@pytest.mark.parametrize("variant", VARIANTS)
 def test_prefill_long_causal_row_sampled_vs_oracle(ops, variant):
     """One 4,160-token causal sequence (Hq 8 / Hkv 1, the TP=8 shape): full oracle compare."""
     L = 4160
@@ -247,6 +250,29 @@ def test_attention_forward_prefix_sharing_same_step(ops):
     assert maxerr(got, want) <= ATOL
     written = ~torch.isnan(kc.float()).any(-1).any(-1)
     assert torch.equal(attn.k_cache.cpu()[written], kc[written])
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "attn_ref_*.pt"))))
+def test_attention_forward_matches_reference_golden(ops, path):
+    """The drop-in `Attention.forward` against the output of the UNMODIFIED reference
+    `Attention.forward` on the same seeded inputs (fixtures from tools/make_golden_gpu.py):
+    attention within 2e-2, cache after the step bit-exact."""
+    from b200attn.layers.attention import Attention
+    from b200attn.utils.context import reset_context, set_context
+    m = torch.load(path)
+    c = make_forward_case(m)
+    Hq, Hkv = m["Hq"], m["Hkv"]
+    attn = Attention(Hq, 128, SCALE, Hkv)
+    attn.k_cache, attn.v_cache = c["k_cache"].cuda(), c["v_cache"].cuda()
+    qkv = c["qkv"].cuda()
+    n = qkv.shape[0]
+    set_context(*[dev(t) for t in c["ctx"]])
+    got = attn(c["q"].cuda(), c["k"].cuda(), qkv[:, (Hq + Hkv) * 128:].view(n, Hkv, 128))
+    reset_context()
+    r = c["num_real"]
+    assert maxerr(got[:r], m["out"][:r]) <= ATOL
+    assert tensor_sha256(attn.k_cache) == m["k_cache_sha256"]
+    assert tensor_sha256(attn.v_cache) == m["v_cache_sha256"]
 
 
 def test_attention_forward_config0_prefill_then_decode(ops):

@@ -8,7 +8,7 @@ import pytest
 import torch
 
 import oracle
-from helpers import GOLDEN, make_paged_case, scatter_inputs
+from helpers import GOLDEN, make_forward_case, make_paged_case, scatter_inputs, tensor_sha256
 
 
 # ----------------------------------------------------------------- scatter (pinned, bit-exact)
@@ -35,6 +35,21 @@ def test_scatter_all_padding_is_noop():
     vc = torch.zeros_like(kc)
     oracle.kv_scatter(k, k, kc, vc, torch.full((4,), -1, dtype=torch.int32))
     assert kc.abs().sum() == 0 and vc.abs().sum() == 0
+
+
+# ----------------------------------------------------------------- attention (pinned on the GPU box)
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "attn_ref_*.pt"))))
+def test_attention_oracle_matches_reference_forward_on_gpu(path):
+    """Fixtures hold the output of the UNMODIFIED reference `Attention.forward` (Triton scatter +
+    flash-attn 2.8.3) run on a B200 by tools/make_golden_gpu.py; inputs are re-created from the seed."""
+    m = torch.load(path)
+    c = make_forward_case(m)
+    o = oracle.attention_forward(c["q"], c["k"], c["v"], c["k_cache"], c["v_cache"], oracle.Context(*c["ctx"]), 128 ** -0.5)
+    n = c["num_real"]
+    assert (o[:n].float() - m["out"][:n].float()).abs().max().item() <= 2e-2      # bf16 tolerance of north_star
+    # the scatter half of the step is bit-exact: digest of the whole cache after the call
+    assert tensor_sha256(c["k_cache"]) == m["k_cache_sha256"]
+    assert tensor_sha256(c["v_cache"]) == m["v_cache_sha256"]
 
 
 # ----------------------------------------------------------------- pointwise (pinned, eager form)
