@@ -1,0 +1,143 @@
+"""The in-scope methods of nanovllm/engine/model_runner.py, re-done for the B200 path
+(SURVEY.md rows a11-a13).  They are bound onto the reference's own `ModelRunner` class by
+`b200attn.install.install()`; everything else of the engine stays the reference's code.
+
+  allocate_kv_cache   model_runner.py:319-375  same tensor, same num_blocks arithmetic (the
+                      reference method itself runs), plus the split-K workspace of the decode
+                      kernel sized once for the largest CUDA-graph bucket so that capture and
+                      replay never allocate.
+  prepare_model_input model_runner.py:400-495  same eight Context fields with the same values
+                      and dtypes; built with numpy instead of per-token Python list appends,
+                      staged in ONE pinned buffer and moved with ONE H2D copy (the reference
+                      makes 7-8 pinned allocations + copies per step).
+  capture_cudagraph   model_runner.py:640-715  unchanged logic (the reference method runs);
+                      the decode kernel it captures reads every length from device memory and
+                      its launch geometry depends on host integers only.
+"""
+import itertools
+
+import numpy as np
+import torch
+
+from .. import ops
+
+_ALIGN = 16
+
+
+def allocate_kv_cache(self, _reference_impl):
+    _reference_impl(self)
+    hf = self.config.hf_config
+    tp = self.world_size
+    num_heads = hf.num_attention_heads // tp
+    num_kv_heads = hf.num_key_value_heads // tp
+    max_bs = max(min(self.config.max_num_seqs, 512), 1)
+    max_blocks = (self.config.max_model_len + self.block_size - 1) // self.block_size
+    ops.reserve_decode_workspace(max_bs, num_heads, num_kv_heads, max_blocks * self.block_size,
+                                 torch.device("cuda", torch.cuda.current_device()))
+
+
+class _Staging:
+    """Two pinned arenas used alternately; an event per arena guards reuse."""
+
+    def __init__(self):
+        self.bufs = [None, None]
+        self.events = [None, None]
+        self.turn = 0
+
+    def get(self, nbytes: int) -> torch.Tensor:
+        self.turn ^= 1
+        i = self.turn
+        if self.events[i] is not None:
+            self.events[i].synchronize()
+        if self.bufs[i] is None or self.bufs[i].numel() < nbytes:
+            self.bufs[i] = torch.empty(max(nbytes * 2, 1 << 16), dtype=torch.uint8, device="cpu", pin_memory=True)
+        return self.bufs[i]
+
+    def sent(self):
+        ev = torch.cuda.Event()
+        ev.record()
+        self.events[self.turn] = ev
+
+
+def build_model_input(seqs, block_size: int):
+    """Pure host part of prepare_model_input: numpy arrays with the reference's values.
+
+    Returns a dict of arrays (block_tables None when sum(k) == sum(q), model_runner.py:483) and
+    the two host ints.  Kept separate from the H2D staging so it is testable on CPU against
+    fixtures generated from the reference's own method (tests/golden/prepare_*.pt)."""
+    n = len(seqs)
+    cached = np.fromiter((s.num_cached_tokens for s in seqs), dtype=np.int64, count=n)
+    new = np.fromiter((s.num_new_tokens for s in seqs), dtype=np.int64, count=n)
+    ctx = cached + new
+    cu_q = np.zeros(n + 1, dtype=np.int64)
+    cu_k = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(new, out=cu_q[1:])
+    np.cumsum(ctx, out=cu_k[1:])
+    total = int(cu_q[-1])
+    tok_seq = np.repeat(np.arange(n, dtype=np.int64), new)               # owning sequence of every new token
+    positions = np.arange(total, dtype=np.int64) - (cu_q[:-1] - cached)[tok_seq]
+    input_ids = np.fromiter(itertools.chain.from_iterable(s[int(c):int(x)] for s, c, x in zip(seqs, cached, ctx)),
+                            dtype=np.int64, count=total)
+    has_table = np.fromiter((1 if s.block_table else 0 for s in seqs), dtype=np.int64, count=n)
+    lens = np.fromiter((len(s) for s in seqs), dtype=np.int64, count=n)
+    need_logits = np.nonzero((lens == ctx) & (has_table == 1))[0].astype(np.int32)
+    width = max((len(s.block_table) for s in seqs), default=0)
+    table = None
+    if width:
+        table = np.full((n, width), -1, dtype=np.int32)
+        for i, s in enumerate(seqs):
+            bt = s.block_table
+            if bt:
+                table[i, :len(bt)] = bt
+    if has_table.all() and total:
+        slot = table[tok_seq, positions // block_size].astype(np.int64) * block_size + positions % block_size
+        slot_mapping = slot.astype(np.int32)
+    else:                                                                 # warmup: sequences without a block table
+        keep = has_table[tok_seq] == 1
+        if keep.any():
+            p, sq = positions[keep], tok_seq[keep]
+            slot_mapping = (table[sq, p // block_size].astype(np.int64) * block_size + p % block_size).astype(np.int32)
+        else:
+            slot_mapping = np.zeros(0, dtype=np.int32)
+    arrays = dict(input_ids=input_ids, positions=positions, cu_seqlens_q=cu_q.astype(np.int32),
+                  cu_seqlens_k=cu_k.astype(np.int32), slot_mapping=slot_mapping, context_lens=ctx.astype(np.int32),
+                  seq_need_compute_logits=need_logits,
+                  block_tables=table if (int(cu_k[-1]) > total and table is not None) else None)
+    return arrays, int(new.max()) if n else 0, int(ctx.max()) if n else 0
+
+
+_ORDER = ("input_ids", "positions", "cu_seqlens_q", "cu_seqlens_k", "slot_mapping", "context_lens",
+          "seq_need_compute_logits", "block_tables")
+
+
+def prepare_model_input(self, seqs, _set_context):
+    arrays, max_q, max_k = build_model_input(seqs, self.block_size)
+    staging = getattr(self, "_b200_staging", None)
+    if staging is None:
+        staging = self._b200_staging = _Staging()
+    offs, nbytes = {}, 0
+    for name in _ORDER:
+        a = arrays[name]
+        if a is None:
+            continue
+        offs[name] = nbytes
+        nbytes += (a.nbytes + _ALIGN - 1) // _ALIGN * _ALIGN
+    host = staging.get(max(nbytes, _ALIGN))
+    host_np = host.numpy()
+    for name, off in offs.items():
+        a = arrays[name]
+        host_np[off:off + a.nbytes] = a.reshape(-1).view(np.uint8)
+    dev = torch.empty(max(nbytes, _ALIGN), dtype=torch.uint8, device="cuda")
+    dev.copy_(host[:max(nbytes, _ALIGN)], non_blocking=True)
+    staging.sent()
+    out = {}
+    for name in _ORDER:
+        a = arrays[name]
+        if a is None:
+            out[name] = None
+            continue
+        dt = torch.int64 if a.dtype == np.int64 else torch.int32
+        out[name] = dev[offs[name]:offs[name] + a.nbytes].view(dt).view(a.shape)
+    _set_context(out["cu_seqlens_q"], out["cu_seqlens_k"], max_q, max_k, out["slot_mapping"], out["context_lens"],
+                 out["block_tables"], out["seq_need_compute_logits"])
+    return out["input_ids"], out["positions"]

@@ -1,0 +1,91 @@
+"""Apply the drop-in to an importable `nanovllm` (the reference, unmodified on disk).
+
+Methods are replaced ON the reference's own classes, so module objects, parameters, attribute
+names (`k_cache`, `v_cache`, `weight`, `cos_sin_cache`, ...) and every `from x import y` binding
+stay valid whatever was imported first:
+
+    nanovllm.layers.attention.Attention.forward        -> scatter + decode / prefill kernels
+    nanovllm.layers.attention.store_kvcache            -> b200_kv_scatter
+    nanovllm.models.qwen3.Qwen3Attention.forward       -> qkv_proj, ONE fused q/k-norm+RoPE launch,
+                                                          attention, o_proj (qwen3.py:183-199 order kept)
+    nanovllm.layers.layernorm.RMSNorm.forward          -> b200_rmsnorm (fused residual add)
+    nanovllm.layers.rotary_embedding.RotaryEmbedding.forward -> rotation-only kernel
+    nanovllm.layers.activation.SiluAndMul.forward      -> b200_silu_and_mul
+    nanovllm.engine.model_runner.ModelRunner.{allocate_kv_cache, prepare_model_input}
+
+`LLM.generate`, `Scheduler`, `BlockManager`, `Sequence`, the linears, the sampler and NCCL are untouched.
+`install(pointwise=False)` limits the patch to attention + scatter; `install(runner=False)`
+leaves ModelRunner alone.
+"""
+import importlib
+
+import torch
+
+from . import ops
+from .layers import attention as _attention
+
+_INSTALLED = False
+
+
+def _attention_forward(self, q, k, v):
+    return _attention.Attention.forward(self, q, k, v)
+
+
+def _qwen3_attention_forward(self, positions, hidden_states):
+    qkv = self.qkv_proj(hidden_states)
+    q, k, v = qkv.split([self.q_size, self.kv_size, self.kv_size], dim=-1)
+    q = q.view(-1, self.num_heads, self.head_dim)
+    k = k.view(-1, self.num_kv_heads, self.head_dim)
+    v = v.view(-1, self.num_kv_heads, self.head_dim)
+    rope = self.rotary_emb
+    if not self.qkv_bias:
+        q, k = ops.qk_norm_rope(q, k, positions, self.q_norm.weight, self.k_norm.weight,
+                                rope.cos_sin_cache, self.q_norm.eps)
+    else:
+        q, k = ops.qk_norm_rope(q, k, positions, None, None, rope.cos_sin_cache)
+    o = self.attn(q, k, v)
+    return self.o_proj(o.flatten(1, -1))
+
+
+def _rmsnorm_forward(self, x, residual=None):
+    xc = x if x.is_contiguous() else x.contiguous()
+    if residual is None:
+        return ops.rms_norm(xc, self.weight, self.eps)
+    return ops.rms_norm(xc, self.weight, self.eps, residual if residual.is_contiguous() else residual.contiguous())
+
+
+def _rotary_forward(self, positions, query, key):
+    return ops.qk_norm_rope(query, key, positions, None, None, self.cos_sin_cache)
+
+
+def _silu_forward(self, x):
+    return ops.silu_and_mul(x if x.is_contiguous() else x.contiguous())
+
+
+def install(pointwise: bool = True, runner: bool = True) -> None:
+    global _INSTALLED
+    if _INSTALLED:
+        return
+    ops.load_library()                                     # fail loudly before touching anything
+    att = importlib.import_module("nanovllm.layers.attention")
+    ctx = importlib.import_module("nanovllm.utils.context")
+    _attention.use_context_getter(ctx.get_context)
+    att.Attention.forward = _attention_forward
+    att.store_kvcache = ops.store_kvcache
+    if pointwise:
+        qwen3 = importlib.import_module("nanovllm.models.qwen3")
+        qwen3.Qwen3Attention.forward = _qwen3_attention_forward
+        importlib.import_module("nanovllm.layers.layernorm").RMSNorm.forward = _rmsnorm_forward
+        importlib.import_module("nanovllm.layers.rotary_embedding").RotaryEmbedding.forward = _rotary_forward
+        importlib.import_module("nanovllm.layers.activation").SiluAndMul.forward = _silu_forward
+    if runner:
+        from .engine import model_runner as ours
+        mr = importlib.import_module("nanovllm.engine.model_runner")
+        ref_alloc = mr.ModelRunner.allocate_kv_cache
+        mr.ModelRunner.allocate_kv_cache = lambda self: ours.allocate_kv_cache(self, ref_alloc)
+        mr.ModelRunner.prepare_model_input = lambda self, seqs: ours.prepare_model_input(self, seqs, ctx.set_context)
+    _INSTALLED = True
+
+
+def installed() -> bool:
+    return _INSTALLED

@@ -1,0 +1,108 @@
+"""E2E HARNESS ONLY (not product code).  tools/e2e_generate.py puts this directory first on
+PYTHONPATH so that every process of a run -- including the reference's spawned TP workers --
+gets the same harness patches, applied identically to BOTH arms (reference and drop-in):
+
+  B200E2E_RANDOM_INIT=<seed>  replace `load_model` (no checkpoints offline) by a seeded
+                              N(0, 0.02) init of every parameter, norm weights = 1
+  B200E2E_GREEDY=1            replace Sampler.forward by argmax and record the top-2 logit margin
+                              of every decision (the reference's sampler forbids greedy, F12)
+  B200E2E_SHM_BYTES=<n>       size of the rank-0 -> worker shared-memory mailbox (F11)
+
+and then chains to the product hook nano-vllm-v1_b200/dropin/sitecustomize.py (B200ATTN_DROPIN)."""
+import atexit
+import importlib.abc
+import importlib.machinery
+import json
+import os
+import runpy
+import sys
+
+_SEED = os.environ.get("B200E2E_RANDOM_INIT")
+_GREEDY = os.environ.get("B200E2E_GREEDY") == "1"
+_TRIGGER = "nanovllm.engine.model_runner"
+_MARGINS = []
+_PER_SEQ = {}
+
+
+def _patch(module):
+    import torch
+    if _SEED is not None:
+        def seeded_init(model, path):
+            g = torch.Generator(device="cuda").manual_seed(int(_SEED))
+            with torch.no_grad():
+                for name, p in sorted(model.named_parameters(), key=lambda kv: kv[0]):
+                    if name.endswith("norm.weight"):
+                        p.fill_(1.0)
+                    else:
+                        # parameters are per-rank shards; parity is checked arm-vs-arm at equal TP, so the
+                        # same seeded draw on every rank of both arms suffices
+                        p.copy_(torch.randn(p.shape, generator=g, device="cuda", dtype=torch.float32).mul_(0.02).to(p.dtype))
+        module.load_model = seeded_init
+    if _GREEDY:
+        sampler = importlib.import_module("nanovllm.layers.sampler")
+
+        def greedy(self, logits, temperatures):
+            top2 = torch.topk(logits.float(), 2, dim=-1)
+            _MARGINS.append((top2.values[:, 0] - top2.values[:, 1]).cpu())
+            return top2.indices[:, 0]
+        sampler.Sampler.forward = greedy
+        orig_run = module.ModelRunner.run
+
+        def run(self, seqs):
+            n0 = len(_MARGINS)
+            result = orig_run(self, seqs)
+            if self.rank == 0 and len(_MARGINS) > n0:                 # attribute this step's margins to seq ids
+                _, need = result
+                rows = need.tolist() if need.numel() else list(range(len(seqs)))
+                m = _MARGINS[-1].tolist()
+                for row, si in enumerate(rows):
+                    _PER_SEQ.setdefault(int(getattr(seqs[si], "seq_id", -1)), []).append(m[row])
+            return result
+        module.ModelRunner.run = run
+        out = os.environ.get("B200E2E_MARGINS_OUT")
+        if out:
+            def dump():
+                if _PER_SEQ:
+                    with open(out, "w") as f:
+                        json.dump({str(k): v for k, v in _PER_SEQ.items()}, f)
+            atexit.register(dump)
+    shm = os.environ.get("B200E2E_SHM_BYTES")
+    if shm:
+        real = module.SharedMemory
+
+        def bigger(name=None, create=False, size=0):
+            return real(name=name, create=create, size=int(shm) if create else size)
+        module.SharedMemory = bigger
+
+
+class _Loader(importlib.abc.Loader):
+    def __init__(self, inner):
+        self.inner = inner
+
+    def create_module(self, spec):
+        return self.inner.create_module(spec)
+
+    def exec_module(self, module):
+        self.inner.exec_module(module)
+        _patch(module)
+
+
+class _Finder(importlib.abc.MetaPathFinder):
+    def find_spec(self, name, path, target=None):
+        if name != _TRIGGER:
+            return None
+        sys.meta_path.remove(self)
+        spec = importlib.util.find_spec(name)        # lets the product hook (if any) wrap first
+        if spec is not None and spec.loader is not None:
+            spec.loader = _Loader(spec.loader)
+        return spec
+
+
+import importlib.util  # noqa: E402
+
+_product = os.path.join(os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))),
+                        "nano-vllm-v1_b200", "dropin", "sitecustomize.py")
+if os.environ.get("B200ATTN_DROPIN") and os.path.exists(_product):
+    runpy.run_path(_product)                         # product hook first ...
+if _SEED is not None or _GREEDY or os.environ.get("B200E2E_SHM_BYTES"):
+    sys.meta_path.insert(0, _Finder())               # ... so the harness finder sits in front and wraps it

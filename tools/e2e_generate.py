@@ -1,0 +1,148 @@
+#!/usr/bin/env python
+"""End-to-end run of the reference's UNTOUCHED `LLM.generate` (offline install under
+baseline/_ref), either as shipped (`--arm reference`: Triton + flash-attn) or with the B200
+drop-in applied (`--arm dropin`).  GPU box only.  One JSON document per run.
+
+    python tools/e2e_generate.py --arm dropin --size 0.6b --num-seqs 256 --in-len 128 --out-len 256 \
+        --chunked-prefill --out gpurun_out/e2e_dropin.json
+    python tools/e2e_generate.py --compare gpurun_out/e2e_reference_greedy.json gpurun_out/e2e_dropin_greedy.json
+
+Both arms get the same harness patches (tools/e2e/sitecustomize.py): seeded random weights and,
+with --greedy, an argmax sampler that records top-2 logit margins.  Throughput = generated tokens /
+wall time of generate(), as the reference's bench.py:26-27 computes it.
+"""
+import argparse
+import json
+import os
+import random
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def launcher(a):
+    env = dict(os.environ)
+    paths = [os.path.join(ROOT, "tools", "e2e"), os.path.join(ROOT, "nano-vllm-v1_b200"),
+             os.environ.get("NANOVLLM_REFERENCE", os.path.join(ROOT, "baseline", "_ref"))]
+    env["PYTHONPATH"] = os.pathsep.join(paths + [env.get("PYTHONPATH", "")])
+    env["B200E2E_RANDOM_INIT"] = str(a.seed)
+    env["B200E2E_SHM_BYTES"] = str(64 << 20)
+    env.pop("B200ATTN_DROPIN", None)
+    if a.arm == "dropin":
+        env["B200ATTN_DROPIN"] = "1"
+    elif a.arm == "dropin-attn":
+        env["B200ATTN_DROPIN"] = "attn"
+    if a.greedy:
+        env["B200E2E_GREEDY"] = "1"
+        env["B200E2E_MARGINS_OUT"] = a.out + ".margins"
+    cmd = [sys.executable, os.path.abspath(__file__), "--worker"] + [x for x in sys.argv[1:] if x != "--worker"]
+    return subprocess.run(cmd, env=env).returncode
+
+
+def worker(a):
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    from make_fake_model import make
+    model_dir = make(a.size, f"/tmp/b200_fake_qwen3_{a.size}_{a.layers or 'full'}", a.layers)
+    import torch
+    from nanovllm import LLM, SamplingParams
+    rnd = random.Random(0)                                                 # as the reference's bench.py:9
+    prompts = [[rnd.randint(0, 10000) for _ in range(a.in_len)] for _ in range(a.num_seqs)]
+    if a.shared_prefix:
+        prefix = [rnd.randint(0, 10000) for _ in range(a.shared_prefix)]
+        prompts = [prefix + p for p in prompts]
+    t0 = time.perf_counter()
+    llm = LLM(model_dir, enforce_eager=a.enforce_eager, max_model_len=a.max_model_len,
+              tensor_parallel_size=a.tp, chunked_prefill=a.chunked_prefill, max_num_seqs=a.max_num_seqs,
+              max_num_batched_tokens=a.max_num_batched_tokens, gpu_memory_utilization=a.gpu_memory_utilization)
+    t_init = time.perf_counter() - t0
+    sp = SamplingParams(temperature=0.6, ignore_eos=True, max_tokens=a.out_len)
+    llm.generate([[1, 2, 3]], SamplingParams(temperature=0.6, ignore_eos=True, max_tokens=4), use_tqdm=False)   # warm-up, bench.py:22
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    outs = llm.generate(prompts, sp, use_tqdm=False)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    import b200attn.install as dropin_mod
+    n_out = sum(len(o["token_ids"]) for o in outs)
+    rec = dict(arm=a.arm, size=a.size, layers=a.layers, tp=a.tp, num_seqs=a.num_seqs, in_len=a.in_len, out_len=a.out_len,
+               shared_prefix=a.shared_prefix, chunked_prefill=a.chunked_prefill, enforce_eager=a.enforce_eager,
+               greedy=a.greedy, seconds=dt, init_seconds=t_init, generated_tokens=n_out, tok_per_s=n_out / dt,
+               total_tok_per_s=(n_out + sum(len(p) for p in prompts)) / dt, dropin_installed=dropin_mod.installed(),
+               gpu=torch.cuda.get_device_name(0), token_ids=[o["token_ids"] for o in outs] if a.greedy else None)
+    os.makedirs(os.path.dirname(os.path.abspath(a.out)), exist_ok=True)
+    with open(a.out, "w") as f:
+        json.dump(rec, f)
+    print(json.dumps({k: v for k, v in rec.items() if k != "token_ids"}), flush=True)
+    llm.exit() if hasattr(llm, "exit") else None
+    return 0
+
+
+def compare(ref_path, our_path, steps, tie_margin):
+    """Greedy parity: token ids must be identical for `steps` decisions per sequence; a sequence may
+    diverge only at a decision whose reference top-2 logit margin is below `tie_margin` (a near-tie
+    that bf16 rounding legitimately flips).  Prints a JSON verdict; exit 1 on a real mismatch."""
+    ref, our = json.load(open(ref_path)), json.load(open(our_path))
+    per_seq = json.load(open(ref_path + ".margins"))                      # seq_id -> margins of its decisions
+    ids = sorted(int(k) for k in per_seq)[-len(ref["token_ids"]):]        # earlier ids belong to the warm-up generate
+    n = len(ref["token_ids"])
+    identical, tie_div, real_div, detail = 0, 0, 0, []
+    all_margins = []
+    for i in range(n):
+        a, b = ref["token_ids"][i][:steps], our["token_ids"][i][:steps]
+        m = per_seq[str(ids[i])][:steps]
+        all_margins.extend(m)
+        if a == b:
+            identical += 1
+            continue
+        j = next(k for k in range(min(len(a), len(b))) if a[k] != b[k])
+        is_tie = m[j] < tie_margin
+        tie_div += is_tie
+        real_div += not is_tie
+        detail.append(dict(seq=i, step=j, ref_margin=round(m[j], 5)))
+    all_margins.sort()
+    verdict = dict(sequences=n, steps=steps, identical=identical, diverged_at_near_tie=tie_div, diverged_for_real=real_div,
+                   tie_margin=tie_margin, first_divergences=detail[:16],
+                   margin_quantiles=dict(p0=all_margins[0], p1=all_margins[len(all_margins) // 100],
+                                         p50=all_margins[len(all_margins) // 2]) if all_margins else None,
+                   ref_tok_per_s=ref.get("tok_per_s"), ours_tok_per_s=our.get("tok_per_s"))
+    print(json.dumps(verdict))
+    return verdict
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--arm", default="dropin", choices=["reference", "dropin", "dropin-attn"])
+    ap.add_argument("--size", default="0.6b")
+    ap.add_argument("--layers", type=int, default=None, help="override num_hidden_layers (memory-bounded runs)")
+    ap.add_argument("--tp", type=int, default=1)
+    ap.add_argument("--num-seqs", type=int, default=256)
+    ap.add_argument("--in-len", type=int, default=128)
+    ap.add_argument("--out-len", type=int, default=256)
+    ap.add_argument("--shared-prefix", type=int, default=0)
+    ap.add_argument("--max-model-len", type=int, default=4096)
+    ap.add_argument("--max-num-seqs", type=int, default=512)
+    ap.add_argument("--max-num-batched-tokens", type=int, default=16384)
+    ap.add_argument("--gpu-memory-utilization", type=float, default=0.9)
+    ap.add_argument("--chunked-prefill", action="store_true")
+    ap.add_argument("--enforce-eager", action="store_true")
+    ap.add_argument("--greedy", action="store_true")
+    ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "e2e.json"))
+    ap.add_argument("--worker", action="store_true")
+    ap.add_argument("--compare", nargs=2)
+    ap.add_argument("--steps", type=int, default=64)
+    ap.add_argument("--tie-margin", type=float, default=0.05)
+    a = ap.parse_args()
+    if a.compare:
+        v = compare(a.compare[0], a.compare[1], a.steps, a.tie_margin)
+        if a.out:
+            with open(a.out, "w") as f:
+                json.dump(v, f)
+        return 1 if v["diverged_for_real"] else 0
+    return worker(a) if a.worker else launcher(a)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -98,11 +98,58 @@ def pointwise_case(name, seed, T, Hq, Hkv, D, inter, max_pos, base=1e6, eps=1e-6
     print("wrote pointwise", name)
 
 
+def prepare_case(name, seed, specs):
+    """Run the reference's ModelRunner.prepare_model_input (model_runner.py:400-495) on CPU: the only
+    CUDA-specific bits are `pin_memory=True` and `.cuda()`, shimmed to no-ops here.
+    specs: list of (num_tokens, num_cached_tokens, num_new_tokens, has_block_table)."""
+    import random
+    from types import SimpleNamespace
+    from nanovllm.engine.model_runner import ModelRunner
+    from nanovllm.engine.sequence import Sequence
+    from nanovllm.utils.context import get_context, reset_context
+    rnd = random.Random(seed)
+    real_tensor, real_cuda = torch.tensor, torch.Tensor.cuda
+    torch.tensor = lambda *a, pin_memory=False, **k: real_tensor(*a, **k)
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    try:
+        seqs, states = [], []
+        free = list(range(4096))
+        rnd.shuffle(free)
+        for (ntok, cached, new, has_bt) in specs:
+            s = Sequence([rnd.randrange(0, 150000) for _ in range(ntok)])
+            s.num_cached_tokens, s.num_new_tokens = cached, new
+            nblk = (cached + new + 255) // 256
+            s.block_table = [free.pop() for _ in range(nblk)] if has_bt else []
+            seqs.append(s)
+            states.append(dict(token_ids=list(s.token_ids), num_cached_tokens=cached, num_new_tokens=new,
+                               block_table=list(s.block_table)))
+        fake = SimpleNamespace(block_size=256)
+        fake.prepare_block_tables = lambda sq: ModelRunner.prepare_block_tables(fake, sq)
+        input_ids, positions = ModelRunner.prepare_model_input(fake, seqs)
+        c = get_context()
+        rec = dict(states=states, input_ids=input_ids, positions=positions, cu_seqlens_q=c.cu_seqlens_q,
+                   cu_seqlens_k=c.cu_seqlens_k, max_seqlen_q=c.max_seqlen_q, max_seqlen_k=c.max_seqlen_k,
+                   slot_mapping=c.slot_mapping, context_lens=c.context_lens, block_tables=c.block_tables,
+                   seq_need_compute_logits=c.seq_need_compute_logits)
+        reset_context()
+    finally:
+        torch.tensor, torch.Tensor.cuda = real_tensor, real_cuda
+    torch.save(rec, os.path.join(OUT, f"prepare_{name}.pt"))
+    print("wrote prepare", name)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     # prefill-like contiguous run, decode-like single rows, graph padding (-1), page crossing
     scatter_case("tp1_prefill", 1, 40, 16, 8, 128, 4, list(range(500, 540)))
     scatter_case("tp8_mixed", 2, 9, 2, 1, 128, 3, [767, -1, 0, 255, 256, -1, 511, 300, 1])
     scatter_case("tp2_decode", 3, 6, 8, 4, 128, 2, [5, 261, 17, -1, 400, 129])
+    # (len(seq), num_cached_tokens, num_new_tokens, has_block_table)
+    prepare_case("pure_prefill", 21, [(128, 0, 128, True), (1, 0, 1, True), (300, 0, 300, True), (257, 0, 257, True)])
+    prepare_case("mixed_chunked", 22, [(700, 512, 188, True), (130, 129, 1, True), (2000, 0, 128, True), (1, 0, 1, True),
+                                       (258, 257, 1, True), (900, 256, 257, True), (64, 0, 64, True), (1040, 1000, 40, True),
+                                       (513, 512, 1, True), (256, 0, 256, True)])
+    prepare_case("decode", 23, [(4096, 4095, 1, True), (2, 1, 1, True), (257, 256, 1, True), (1301, 1300, 1, True)])
+    prepare_case("warmup", 24, [(600, 0, 600, False), (600, 0, 600, False)])
     pointwise_case("q0p6b", 11, 7, 16, 8, 128, 96, 4096)
     pointwise_case("tp8_14b", 12, 5, 5, 1, 128, 64, 40960)
