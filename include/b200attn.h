@@ -108,6 +108,39 @@ int b200_attn_prefill(const void* q, int64_t q_token_stride,
                       int32_t variant, void* stream);
 
 /* ---------------------------------------------------------------------------------
+ * (2'/3') Planned varlen attention for mixed batches.  The reference hands
+ *     flash_attn_varlen_func one call per layer whatever the mix of rows (attention.py:242-248);
+ *     here a step plan built ON THE DEVICE from cu_seqlens routes
+ *       rows with q_len > 1  -> persistent tcgen05 prefill kernel (work list sorted heaviest-first),
+ *       rows with q_len == 1 -> split-K decode kernel (only when a block table exists),
+ *     and is reused by every layer of the step.  No host reads, graph-capturable.
+ *     plan: b200_attn_plan_bytes(batch, total_q) bytes of device memory, 16-byte aligned.
+ *     b200_attn_prefill_planned / b200_attn_decode_varlen write disjoint rows of `out`.
+ */
+size_t b200_attn_plan_bytes(int32_t batch, int32_t total_q);
+int b200_attn_plan(const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k, int32_t batch, int32_t total_q,
+                   int32_t route_decode, void* plan, size_t plan_bytes, void* stream);
+int b200_attn_prefill_planned(const void* q, int64_t q_token_stride,
+                              const void* k, const void* v,
+                              int64_t k_token_stride, int64_t v_token_stride,
+                              void* out, int64_t out_token_stride,
+                              const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
+                              const int32_t* block_tables, int32_t bt_row_stride,
+                              int32_t batch, int32_t total_q, int32_t max_seqlen_q, int32_t max_seqlen_k,
+                              int32_t num_heads, int32_t num_kv_heads, int32_t head_dim,
+                              int32_t page_size, int64_t num_cache_blocks, float softmax_scale,
+                              const void* plan, size_t plan_bytes, void* stream);
+int b200_attn_decode_varlen(const void* q, int64_t q_token_stride,
+                            const void* k_cache, const void* v_cache,
+                            void* out, int64_t out_token_stride,
+                            const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
+                            const int32_t* block_tables, int32_t bt_row_stride,
+                            int32_t batch, int32_t num_heads, int32_t num_kv_heads,
+                            int32_t head_dim, int32_t page_size, float softmax_scale,
+                            int32_t num_splits, void* workspace, size_t workspace_bytes,
+                            const void* plan, size_t plan_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------
  * (4a) Fused per-head RMSNorm + RoPE on q and k.  Replaces q_norm/k_norm
  *      (layers/layernorm.py:57-93 via models/qwen3.py:191-193) followed by
  *      RotaryEmbedding.forward (layers/rotary_embedding.py:114-153), keeping the two

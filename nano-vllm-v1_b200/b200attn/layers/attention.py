@@ -7,8 +7,10 @@ Dispatch (attention.py:214-249):
     cu_seqlens_q is None       -> paged decode, graph form                   (piece 3)
     else, max_seqlen_q == 1
           and block_tables     -> paged decode, eager form (same kernel)     (piece 3)
-    else block_tables present  -> paged varlen prefill                       (piece 2)
-    else                       -> unpaged varlen prefill on fresh k, v       (piece 2)
+    else                       -> step plan (built once per step on the device, cached on the
+                                  Context): rows with q_len > 1 -> persistent tcgen05 prefill
+                                  (piece 2, paged over block_tables or unpaged on fresh k, v);
+                                  rows with q_len == 1 of a paged call -> decode kernel (piece 3)
 The scatter is a separate launch, stream-ordered before any read, because sequences scheduled
 in the same step may read prefix blocks another sequence writes in that step.
 """
@@ -17,7 +19,10 @@ from torch import nn
 
 from .. import ops
 
+import os
+
 _get_context = None
+_PREFILL_VARIANT = {"mma": 1, "tc": 2, "tc1": 3}.get(os.environ.get("B200ATTN_PREFILL", ""))
 
 
 def _context():
@@ -62,6 +67,18 @@ class Attention(nn.Module):
                 # eager decode (bs > 512 or enforce_eager): every row has exactly one query token
                 return ops.attn_decode(q, k_cache, v_cache, context.context_lens, context.block_tables, self.scale)
             k, v = k_cache, v_cache
-        return ops.attn_varlen(q, k, v, context.cu_seqlens_q, context.cu_seqlens_k,
-                               context.max_seqlen_q, context.max_seqlen_k, self.scale,
-                               block_table=context.block_tables)
+        if _PREFILL_VARIANT is not None:                      # B200ATTN_PREFILL=mma|tc: unplanned kernels (debug/bench)
+            return ops.attn_varlen(q, k, v, context.cu_seqlens_q, context.cu_seqlens_k,
+                                   context.max_seqlen_q, context.max_seqlen_k, self.scale,
+                                   block_table=context.block_tables, variant=_PREFILL_VARIANT)
+        plan = getattr(context, "_b200_plan", None)
+        if plan is None or plan.total_q != q.shape[0]:
+            plan = ops.attn_plan(context.cu_seqlens_q, context.cu_seqlens_k, q.shape[0],
+                                 route_decode=context.block_tables is not None)
+            try:
+                context._b200_plan = plan                     # every layer of this step reuses it
+            except AttributeError:
+                pass
+        return ops.attn_varlen_planned(q, k, v, context.cu_seqlens_q, context.cu_seqlens_k,
+                                       context.max_seqlen_q, context.max_seqlen_k, self.scale,
+                                       block_table=context.block_tables, plan=plan)

@@ -164,6 +164,80 @@ def attn_varlen(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens_q:
     return out
 
 
+# ------------------------------------------------------------------------------------ (2'/3')
+class StepPlan:
+    """Device-built routing of one varlen step (b200_attn_plan): work list of the persistent
+    prefill kernel + list of single-token rows for the decode kernel.  Built once per engine step
+    and shared by every layer (the Context it is derived from is the same for all layers)."""
+
+    def __init__(self, buf: torch.Tensor, batch: int, total_q: int, route_decode: bool) -> None:
+        self.buf, self.batch, self.total_q, self.route_decode = buf, batch, total_q, route_decode
+
+    def counts(self):
+        """(prefill work items, decode rows) -- synchronises; for tests and tools only."""
+        head = self.buf[:8].view(torch.int32).cpu()
+        return int(head[0]), int(head[1])
+
+
+def attn_plan(cu_seqlens_q: torch.Tensor, cu_seqlens_k: torch.Tensor, total_q: int, route_decode: bool) -> StepPlan:
+    _need_i32(cu_seqlens_q, "cu_seqlens_q")
+    _need_i32(cu_seqlens_k, "cu_seqlens_k")
+    B = cu_seqlens_q.numel() - 1
+    lib = load_library()
+    nbytes = lib.b200_attn_plan_bytes(max(B, 1), total_q)
+    buf = torch.empty(nbytes, dtype=torch.uint8, device=cu_seqlens_q.device)
+    check(lib.b200_attn_plan(cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr(), B, total_q, 1 if route_decode else 0,
+                             buf.data_ptr(), nbytes, _stream()), "b200_attn_plan")
+    return StepPlan(buf, B, total_q, route_decode)
+
+
+def attn_varlen_planned(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens_q: torch.Tensor,
+                        cu_seqlens_k: torch.Tensor, max_seqlen_q: int, max_seqlen_k: int, scale: float,
+                        block_table: Optional[torch.Tensor] = None, plan: Optional[StepPlan] = None,
+                        out: Optional[torch.Tensor] = None, num_splits: Optional[int] = None) -> torch.Tensor:
+    """flash_attn_varlen_func(..., causal=True, block_table=...) semantics (attention.py:242-248) through
+    the step plan: multi-token rows on the persistent tcgen05 kernel, single-token rows (paged calls
+    only) on the split-K decode kernel."""
+    T, Hq, D = q.shape
+    for t, n in ((q, "q"), (k, "k"), (v, "v")):
+        _need_cuda_bf16(t, n)
+    assert q.stride(-1) == 1 and q.stride(1) == D
+    B = cu_seqlens_q.numel() - 1
+    paged = block_table is not None
+    if plan is None:
+        plan = attn_plan(cu_seqlens_q, cu_seqlens_k, T, route_decode=paged)
+    assert plan.batch == B and plan.total_q == T and (not plan.route_decode or paged)
+    if paged:
+        _need_i32(block_table, "block_table")
+        assert k.dim() == 4 and k.is_contiguous() and v.is_contiguous() and k.shape[1] == PAGE
+        assert block_table.shape[0] == B
+        Hkv, ks, vs, nblocks = k.shape[2], 0, 0, k.shape[0]
+        bt_ptr, bt_stride = block_table.data_ptr(), block_table.stride(0)
+    else:
+        assert k.dim() == 3 and k.stride(-1) == 1 and v.stride(-1) == 1 and k.stride(1) == D and v.stride(1) == D
+        Hkv, ks, vs, nblocks = k.shape[1], k.stride(0), v.stride(0), 0
+        bt_ptr, bt_stride = None, 0
+    if out is None:
+        out = torch.empty((T, Hq, D), dtype=q.dtype, device=q.device)
+    lib = load_library()
+    if max_seqlen_q > 1:
+        check(lib.b200_attn_prefill_planned(q.data_ptr(), q.stride(0), k.data_ptr(), v.data_ptr(), ks, vs,
+                                            out.data_ptr(), out.stride(0), cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr(),
+                                            bt_ptr, bt_stride, B, T, int(max_seqlen_q), int(max_seqlen_k), Hq, Hkv, D, PAGE,
+                                            nblocks, float(scale), plan.buf.data_ptr(), plan.buf.numel(), _stream()),
+              "b200_attn_prefill_planned")
+    if plan.route_decode:
+        if num_splits is None:
+            num_splits = lib.b200_decode_plan(B, Hkv, int(max_seqlen_k))
+        ws = _workspace_for(B, Hq, num_splits, q.device)
+        check(lib.b200_attn_decode_varlen(q.data_ptr(), q.stride(0), k.data_ptr(), v.data_ptr(), out.data_ptr(), out.stride(0),
+                                          cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr(), bt_ptr, bt_stride, B, Hq, Hkv, D,
+                                          PAGE, float(scale), num_splits, ws.data_ptr() if ws is not None else None,
+                                          ws.numel() if ws is not None else 0, plan.buf.data_ptr(), plan.buf.numel(),
+                                          _stream()), "b200_attn_decode_varlen")
+    return out
+
+
 # ------------------------------------------------------------------------------------ (4)
 def qk_norm_rope(q: torch.Tensor, k: torch.Tensor, positions: torch.Tensor, q_weight: Optional[torch.Tensor],
                  k_weight: Optional[torch.Tensor], cos_sin_cache: torch.Tensor, eps: float = 1e-6) -> Tuple[torch.Tensor, torch.Tensor]:

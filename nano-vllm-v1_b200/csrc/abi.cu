@@ -159,6 +159,82 @@ int b200_attn_prefill(const void* q, int64_t q_token_stride, const void* k, cons
     return launch_attn_prefill_mma(a, (cudaStream_t)stream);
 }
 
+size_t b200_attn_plan_bytes(int32_t batch, int32_t total_q) {
+    if (batch <= 0 || total_q < 0) return 0;
+    return (plan_bytes(batch, total_q) + 15) & ~(size_t)15;
+}
+
+int b200_attn_plan(const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k, int32_t batch, int32_t total_q,
+                   int32_t route_decode, void* plan, size_t plan_bytes_given, void* stream) {
+    if (batch < 0 || total_q < 0) return B200_ERR_RANGE;
+    if (!cu_seqlens_q || !cu_seqlens_k || !plan) return B200_ERR_NULL;
+    if (!aligned16(plan)) return B200_ERR_ALIGN;
+    if (plan_bytes_given < plan_bytes(batch > 0 ? batch : 1, total_q)) return B200_ERR_WORKSPACE;
+    return launch_attn_plan(cu_seqlens_q, cu_seqlens_k, batch, route_decode ? 1 : 0, (int32_t*)plan,
+                            plan_max_items(batch, total_q), (cudaStream_t)stream);
+}
+
+int b200_attn_prefill_planned(const void* q, int64_t q_token_stride, const void* k, const void* v,
+                              int64_t k_token_stride, int64_t v_token_stride, void* out, int64_t out_token_stride,
+                              const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
+                              const int32_t* block_tables, int32_t bt_row_stride,
+                              int32_t batch, int32_t total_q, int32_t max_seqlen_q, int32_t max_seqlen_k,
+                              int32_t num_heads, int32_t num_kv_heads, int32_t head_dim, int32_t page_size,
+                              int64_t num_cache_blocks, float softmax_scale,
+                              const void* plan, size_t plan_bytes_given, void* stream) {
+    if (batch < 0 || total_q < 0 || max_seqlen_q < 0 || max_seqlen_k < 0) return B200_ERR_RANGE;
+    if (batch == 0 || total_q == 0) return B200_OK;
+    if (!q || !k || !v || !out || !cu_seqlens_q || !cu_seqlens_k || !plan) return B200_ERR_NULL;
+    if (head_dim != B200_HD_CONST || (block_tables && page_size != 256) || num_kv_heads <= 0 ||
+        num_heads % num_kv_heads != 0)
+        return B200_ERR_SHAPE;
+    if (!aligned16(q) || !aligned16(k) || !aligned16(v) || !aligned16(out) || !stride_ok(q_token_stride) ||
+        !stride_ok(out_token_stride) || (!block_tables && (!stride_ok(k_token_stride) || !stride_ok(v_token_stride))))
+        return B200_ERR_ALIGN;
+    if (plan_bytes_given < plan_bytes(batch, total_q)) return B200_ERR_WORKSPACE;
+    if (!prefill_tc_available()) return B200_ERR_UNAVAILABLE;
+    PrefillArgs a;
+    a.q = q; a.q_token_stride = q_token_stride; a.k = k; a.v = v;
+    a.k_token_stride = k_token_stride; a.v_token_stride = v_token_stride;
+    a.out = out; a.out_token_stride = out_token_stride; a.cu_q = cu_seqlens_q; a.cu_k = cu_seqlens_k;
+    a.block_tables = block_tables; a.bt_row_stride = bt_row_stride;
+    a.batch = batch; a.total_q = total_q; a.max_q = max_seqlen_q; a.max_k = max_seqlen_k;
+    a.Hq = num_heads; a.Hkv = num_kv_heads; a.num_cache_blocks = num_cache_blocks; a.scale = softmax_scale;
+    return launch_attn_prefill_persist(a, (const int32_t*)plan, plan_max_items(batch, total_q), (cudaStream_t)stream);
+}
+
+int b200_attn_decode_varlen(const void* q, int64_t q_token_stride, const void* k_cache, const void* v_cache,
+                            void* out, int64_t out_token_stride, const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
+                            const int32_t* block_tables, int32_t bt_row_stride,
+                            int32_t batch, int32_t num_heads, int32_t num_kv_heads, int32_t head_dim, int32_t page_size,
+                            float softmax_scale, int32_t num_splits, void* workspace, size_t workspace_bytes,
+                            const void* plan, size_t plan_bytes_given, void* stream) {
+    if (batch < 0 || num_splits < 1 || bt_row_stride < 0) return B200_ERR_RANGE;
+    if (batch == 0) return B200_OK;
+    if (!q || !k_cache || !v_cache || !out || !cu_seqlens_q || !cu_seqlens_k || !block_tables || !plan) return B200_ERR_NULL;
+    if (head_dim != B200_HD_CONST || page_size != 256 || num_kv_heads <= 0 || num_heads % num_kv_heads != 0 ||
+        num_heads / num_kv_heads > 16)
+        return B200_ERR_SHAPE;
+    if (!aligned16(q) || !aligned16(k_cache) || !aligned16(v_cache) || !aligned16(out) ||
+        !stride_ok(q_token_stride) || !stride_ok(out_token_stride))
+        return B200_ERR_ALIGN;
+    const size_t need = b200_decode_workspace_bytes(batch, num_heads, num_splits);
+    if (num_splits > 1 && (!workspace || workspace_bytes < need)) return B200_ERR_WORKSPACE;
+    if (plan_bytes_given < (size_t)PLAN_HEADER_WORDS * 4 + (size_t)batch * 4) return B200_ERR_WORKSPACE;
+    DecodeArgs a;
+    a.q = q; a.q_token_stride = q_token_stride; a.k_cache = k_cache; a.v_cache = v_cache;
+    a.out = out; a.out_token_stride = out_token_stride; a.context_lens = nullptr;
+    a.block_tables = block_tables; a.bt_row_stride = bt_row_stride;
+    a.batch = batch; a.Hq = num_heads; a.Hkv = num_kv_heads; a.scale = softmax_scale; a.num_splits = num_splits;
+    a.ws_o = (float*)workspace;
+    a.ws_lse = workspace ? (float*)workspace + (size_t)batch * num_splits * num_heads * B200_HD_CONST : nullptr;
+    const int32_t* pl = (const int32_t*)plan;
+    a.cu_q = cu_seqlens_q; a.cu_k = cu_seqlens_k;
+    a.n_rows = pl + 1;
+    a.row_list = pl + PLAN_HEADER_WORDS;
+    return launch_attn_decode(a, (cudaStream_t)stream);
+}
+
 int b200_qk_norm_rope(const void* q, int64_t q_token_stride, const void* k, int64_t k_token_stride,
                       const int64_t* positions, const float* cos_sin_cache, const void* q_weight,
                       const void* k_weight, float eps, void* q_out, void* k_out,

@@ -41,7 +41,25 @@ struct DecodeParams {
     const int32_t* context_lens; const int32_t* block_tables; int32_t bt_row_stride;
     int32_t Hq, Hkv, G; float scale_log2; int32_t num_splits;
     float* ws_o; float* ws_lse;
+    // varlen form (mixed batches): rows come from a device-built list, lengths from cu_seqlens
+    const int32_t* cu_q; const int32_t* cu_k; const int32_t* row_list; const int32_t* n_rows;
 };
+
+// Resolve (list index -> sequence, its context length, the token index of its single query).
+struct DecodeRow { int b, L, tok; bool valid; };
+__device__ __forceinline__ DecodeRow decode_row(const DecodeParams& p, int idx) {
+    DecodeRow r;
+    r.valid = true;
+    if (p.row_list != nullptr) {
+        if (idx >= __ldg(p.n_rows)) { r.valid = false; r.b = 0; r.L = 0; r.tok = 0; return r; }
+        r.b = __ldg(p.row_list + idx);
+        r.L = __ldg(p.cu_k + r.b + 1) - __ldg(p.cu_k + r.b);
+        r.tok = __ldg(p.cu_q + r.b);
+    } else {
+        r.b = idx; r.L = p.context_lens[idx]; r.tok = idx;
+    }
+    return r;
+}
 
 __global__ void __launch_bounds__(DEC_THREADS, 2) paged_decode_kernel(const DecodeParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -50,9 +68,12 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) paged_decode_kernel(const Deco
     const int s = blockIdx.x % S;
     const int bh = blockIdx.x / S;
     const int h = bh % p.Hkv;
-    const int b = bh / p.Hkv;
+    const int bi = bh / p.Hkv;                                  // row index (workspace slot)
     const int G = p.G;
-    const int L = p.context_lens[b];
+    const DecodeRow row = decode_row(p, bi);
+    if (!row.valid) return;
+    const int b = row.b, L = row.L;
+    const int64_t tok = row.tok;
 
     const int chunks_total = (L + DEC_TOK - 1) / DEC_TOK;
     const int n_eff = dec_eff_splits(L, S);
@@ -63,9 +84,9 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) paged_decode_kernel(const Deco
     if (c_begin >= c_end) {                                   // empty split or padding row (len 0)
         if (S == 1) {
             for (int r = 0; r < G; ++r)
-                p.out[(int64_t)b * p.out_token_stride + (int64_t)(h * G + r) * B200_HD + threadIdx.x] = __float2bfloat16(0.f);
+                p.out[tok * p.out_token_stride + (int64_t)(h * G + r) * B200_HD + threadIdx.x] = __float2bfloat16(0.f);
         } else if (threadIdx.x < G) {
-            p.ws_lse[((int64_t)b * S + s) * p.Hq + h * G + threadIdx.x] = -INFINITY;
+            p.ws_lse[((int64_t)bi * S + s) * p.Hq + h * G + threadIdx.x] = -INFINITY;
         }
         return;
     }
@@ -74,7 +95,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) paged_decode_kernel(const Deco
     const int r0 = lane >> 2, r1 = r0 + 8, cq = (lane & 3) * 2;
     uint32_t qa[8][4];
     {
-        const __nv_bfloat16* qb = p.q + (int64_t)b * p.q_token_stride + (int64_t)h * G * B200_HD;
+        const __nv_bfloat16* qb = p.q + tok * p.q_token_stride + (int64_t)h * G * B200_HD;
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks) {
             qa[ks][0] = r0 < G ? *reinterpret_cast<const uint32_t*>(qb + r0 * B200_HD + ks * 16 + cq) : 0u;
@@ -227,9 +248,9 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) paged_decode_kernel(const Deco
         const float val = acc / den;
         const int head = h * G + r;
         if (S == 1) {
-            p.out[(int64_t)b * p.out_token_stride + (int64_t)head * B200_HD + t] = __float2bfloat16_rn(val);
+            p.out[tok * p.out_token_stride + (int64_t)head * B200_HD + t] = __float2bfloat16_rn(val);
         } else {
-            const int64_t idx = ((int64_t)b * S + s) * p.Hq + head;
+            const int64_t idx = ((int64_t)bi * S + s) * p.Hq + head;
             p.ws_o[idx * B200_HD + t] = val;
             if (t == 0) p.ws_lse[idx] = ms + log2f(den);
         }
@@ -238,10 +259,12 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) paged_decode_kernel(const Deco
 
 // Merge the splits of one (sequence, head): out = sum_s 2^(lse_s - max) o_s / sum_s 2^(lse_s - max).
 __global__ void __launch_bounds__(B200_HD) decode_reduce_kernel(const DecodeParams p, int32_t batch) {
-    const int b = blockIdx.x / p.Hq, head = blockIdx.x % p.Hq, t = threadIdx.x;
+    const int bi = blockIdx.x / p.Hq, head = blockIdx.x % p.Hq, t = threadIdx.x;
     const int S = p.num_splits;
-    const int n_eff = dec_eff_splits(p.context_lens[b], S);
-    const float* lse = p.ws_lse + ((int64_t)b * S) * p.Hq + head;
+    const DecodeRow row = decode_row(p, bi);
+    if (!row.valid) return;
+    const int n_eff = dec_eff_splits(row.L, S);
+    const float* lse = p.ws_lse + ((int64_t)bi * S) * p.Hq + head;
     float mx = -INFINITY;
     for (int s = 0; s < n_eff; ++s) mx = fmaxf(mx, lse[(int64_t)s * p.Hq]);
     float acc = 0.f, den = 0.f;
@@ -250,12 +273,12 @@ __global__ void __launch_bounds__(B200_HD) decode_reduce_kernel(const DecodePara
             const float ls = lse[(int64_t)s * p.Hq];
             if (ls == -INFINITY) continue;
             const float w = fast_exp2(ls - mx);
-            acc += w * p.ws_o[(((int64_t)b * S + s) * p.Hq + head) * B200_HD + t];
+            acc += w * p.ws_o[(((int64_t)bi * S + s) * p.Hq + head) * B200_HD + t];
             den += w;
         }
     }
     const float val = den > 0.f ? acc / den : 0.f;
-    p.out[(int64_t)b * p.out_token_stride + (int64_t)head * B200_HD + t] = __float2bfloat16_rn(val);
+    p.out[(int64_t)row.tok * p.out_token_stride + (int64_t)head * B200_HD + t] = __float2bfloat16_rn(val);
 }
 
 int launch_attn_decode(const DecodeArgs& a, cudaStream_t stream) {
@@ -273,6 +296,7 @@ int launch_attn_decode(const DecodeArgs& a, cudaStream_t stream) {
     p.Hq = a.Hq; p.Hkv = a.Hkv; p.G = a.Hq / a.Hkv;
     p.scale_log2 = a.scale * 1.4426950408889634f;
     p.num_splits = a.num_splits; p.ws_o = a.ws_o; p.ws_lse = a.ws_lse;
+    p.cu_q = a.cu_q; p.cu_k = a.cu_k; p.row_list = a.row_list; p.n_rows = a.n_rows;
     if (a.batch == 0) return 0;
     const int64_t grid = (int64_t)a.batch * a.Hkv * a.num_splits;
     paged_decode_kernel<<<(unsigned)grid, DEC_THREADS, DEC_SMEM_BYTES, stream>>>(p);

@@ -1,0 +1,83 @@
+// Step plan for varlen attention calls (mixed prefill + decode batches).
+//
+// One tiny kernel, run ONCE per engine step (every layer of the step reuses its output), turns
+// cu_seqlens_q/k into
+//   * a work list for the persistent tcgen05 prefill kernel: one item per 256-row query tile
+//     of a sequence with q_len > 1 (or every sequence when routing is off), ordered by
+//     descending number of KV tiles (longest-processing-time-first for the static round-robin
+//     over the persistent CTAs);
+//   * the list of rows with exactly one query token, which go to the split-K decode kernel
+//     (a 128-row UMMA tile would be <1 % utilised by such a row).
+// Everything stays on the device: no host read of lengths, so the call is graph-capturable.
+//
+// The reference has no counterpart: flash-attn schedules inside its own launch
+// (attention.py:242-248 passes only cu_seqlens and max_seqlen).
+#include "common.cuh"
+#include "launch.h"
+
+namespace b200 {
+
+constexpr int PLAN_THREADS = 1024;
+constexpr int PLAN_MAX_KEY = 2047;
+
+__global__ void __launch_bounds__(PLAN_THREADS) attn_plan_kernel(
+    const int32_t* __restrict__ cu_q, const int32_t* __restrict__ cu_k, int32_t batch, int32_t route_decode,
+    int32_t* __restrict__ plan, int32_t max_items) {
+    __shared__ int32_t hist[PLAN_MAX_KEY + 1];
+    __shared__ int32_t n_decode;
+    for (int i = threadIdx.x; i <= PLAN_MAX_KEY; i += PLAN_THREADS) hist[i] = 0;
+    if (threadIdx.x == 0) n_decode = 0;
+    __syncthreads();
+    int32_t* decode_rows = plan + PLAN_HEADER_WORDS;
+    int32_t* items = decode_rows + batch;
+
+    auto key_of = [](int mt, int Lq, int Lk) {
+        const int kv_end = min(Lk, (mt + 1) * PLAN_TILE_ROWS + (Lk - Lq));
+        const int k = (kv_end + 127) / 128;
+        return min(max(k, 0), PLAN_MAX_KEY);
+    };
+    // pass 1: histogram of tile costs; single-token rows go to the decode list
+    for (int b = threadIdx.x; b < batch; b += PLAN_THREADS) {
+        const int Lq = cu_q[b + 1] - cu_q[b], Lk = cu_k[b + 1] - cu_k[b];
+        if (Lq <= 0) continue;
+        if (route_decode && Lq == 1) {
+            decode_rows[atomicAdd(&n_decode, 1)] = b;
+            continue;
+        }
+        const int tiles = (Lq + PLAN_TILE_ROWS - 1) / PLAN_TILE_ROWS;
+        for (int mt = 0; mt < tiles; ++mt) atomicAdd(&hist[key_of(mt, Lq, Lk)], 1);
+    }
+    __syncthreads();
+    // descending exclusive scan (serial over 2048 bins by one warp's lane 0 is ~2 us; fine once per step)
+    if (threadIdx.x == 0) {
+        int run = 0;
+        for (int k = PLAN_MAX_KEY; k >= 0; --k) {
+            const int c = hist[k];
+            hist[k] = run;
+            run += c;
+        }
+        plan[0] = run;                       // number of prefill work items
+        plan[1] = n_decode;                  // number of single-token rows
+        plan[2] = 0;
+        plan[3] = 0;
+    }
+    __syncthreads();
+    // pass 2: scatter the items to their sorted positions
+    for (int b = threadIdx.x; b < batch; b += PLAN_THREADS) {
+        const int Lq = cu_q[b + 1] - cu_q[b], Lk = cu_k[b + 1] - cu_k[b];
+        if (Lq <= 0 || (route_decode && Lq == 1)) continue;
+        const int tiles = (Lq + PLAN_TILE_ROWS - 1) / PLAN_TILE_ROWS;
+        for (int mt = tiles - 1; mt >= 0; --mt) {
+            const int pos = atomicAdd(&hist[key_of(mt, Lq, Lk)], 1);
+            if (pos < max_items) { items[2 * pos] = b; items[2 * pos + 1] = mt; }
+        }
+    }
+}
+
+int launch_attn_plan(const int32_t* cu_q, const int32_t* cu_k, int32_t batch, int32_t route_decode,
+                     int32_t* plan, int32_t max_items, cudaStream_t stream) {
+    attn_plan_kernel<<<1, PLAN_THREADS, 0, stream>>>(cu_q, cu_k, batch, route_decode, plan, max_items);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace b200

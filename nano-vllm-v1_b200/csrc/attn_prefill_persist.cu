@@ -1,0 +1,441 @@
+// (2, variant 4) Persistent varlen causal prefill / chunked prefill on Blackwell tensor cores.
+//
+// Same tile math as attn_prefill_tc.cu (TMA-staged Q/K/V, tcgen05.mma with S and O in TMEM, P fed
+// back to the tensor core from TMEM, two 128-row query tiles ping-ponging per CTA), restructured
+// around a device-built work list (attn_plan.cu):
+//   * one CTA per SM loops over work units (256-row query tile of one sequence x one q head) taken
+//     round-robin from a list sorted by descending KV length, so a causal batch is load-balanced
+//     and rows with a single query token never reach this kernel (they go to the decode kernel);
+//   * barrier phases run on counters that survive across units, so the producer prefetches the
+//     next unit's Q/K/V while the current unit drains and TMEM/smem/barriers are set up once;
+//   * setmaxnreg moves registers from the producer/MMA warps to the softmax warpgroups
+//     (a softmax thread keeps its whole 128-column score row in registers, no spills);
+//   * softmax issue slots are cut with packed f32x2 FMA/ADD, 3-input max and a single FFMA that
+//     folds scale and row maximum into the exponent argument.
+//
+// Warp roles (384 threads): warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM allocator,
+// warp 3 idle, warps 4-7 / 8-11 softmax + correction + epilogue of query tile 0 / 1.
+//
+// Replaces flash_attn_varlen_func (attention.py:242-248), paged and unpaged.
+#include "launch.h"
+#include "tc_ptx.cuh"
+
+namespace b200 {
+
+struct PersistParams {
+    const int32_t* cu_q; const int32_t* cu_k; const int32_t* block_tables; int32_t bt_row_stride;
+    __nv_bfloat16* out; int64_t out_token_stride;
+    int32_t Hq, G; float scale_log2;
+    const int32_t* plan; const int32_t* items;
+};
+
+struct PsSmem {
+    static constexpr int NQ = 2;
+    static constexpr int Q_OFF = 0;
+    static constexpr int K_OFF = Q_OFF + NQ * TC_TILE_BYTES;
+    static constexpr int V_OFF = K_OFF + TC_KV_STAGES * TC_TILE_BYTES;
+    static constexpr int BAR_OFF = V_OFF + TC_KV_STAGES * TC_TILE_BYTES;
+    // q_full[2] q_empty[2] k_full[S] k_empty[S] v_full[S] v_empty[S] s_full[2] p_full[2] o_final[2]
+    static constexpr int NUM_BARS = 5 * NQ + 4 * TC_KV_STAGES;
+    static constexpr int TMEM_PTR_OFF = BAR_OFF + NUM_BARS * 8;
+    static constexpr int TOTAL = TMEM_PTR_OFF + 16;
+    static constexpr int ALLOC = TOTAL + 1024;
+};
+
+struct Unit {
+    int b, head, q0, Lq, k0, Lk, m0, n_t0, n_t1, n_max;
+    __device__ __forceinline__ int nt(int t) const { return t == 0 ? n_t0 : n_t1; }
+};
+
+// Work unit w of this launch: (item w / Hq, head w % Hq).  Every role evaluates this itself.
+__device__ __forceinline__ bool get_unit(const PersistParams& p, int w, Unit& u) {
+    const int n_items = __ldg(p.plan);
+    if (w >= n_items * p.Hq) return false;
+    const int item = w / p.Hq;
+    u.head = w - item * p.Hq;
+    u.b = __ldg(p.items + 2 * item);
+    const int mt = __ldg(p.items + 2 * item + 1);
+    u.q0 = __ldg(p.cu_q + u.b);
+    u.Lq = __ldg(p.cu_q + u.b + 1) - u.q0;
+    u.k0 = __ldg(p.cu_k + u.b);
+    u.Lk = __ldg(p.cu_k + u.b + 1) - u.k0;
+    u.m0 = mt * PLAN_TILE_ROWS;
+    const int offset = u.Lk - u.Lq;
+    int kv_end0 = min(u.Lk, u.m0 + TC_BM + offset);
+    if (u.m0 >= u.Lq || kv_end0 < 0) kv_end0 = 0;
+    int kv_end1 = min(u.Lk, u.m0 + 2 * TC_BM + offset);
+    if (u.m0 + TC_BM >= u.Lq || kv_end1 < 0) kv_end1 = 0;
+    u.n_t0 = (kv_end0 + TC_BN - 1) / TC_BN;
+    u.n_t1 = (kv_end1 + TC_BN - 1) / TC_BN;
+    u.n_max = max(u.n_t0, u.n_t1);
+    return true;
+}
+
+// ---- packed f32x2 arithmetic (sm_100: FFMA2 / FADD2) and 3-input max ---------------------------
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ float max3(float a, float b, float c) {
+    float d;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+__device__ __forceinline__ uint32_t cvt_bf16x2(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+
+__global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
+    const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
+    const __grid_constant__ CUtensorMap map_v, const PersistParams p) {
+    using L = PsSmem;
+    constexpr int S = TC_KV_STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    const uint32_t sQ = smem_base + L::Q_OFF, sK = smem_base + L::K_OFF, sV = smem_base + L::V_OFF;
+    const uint32_t bars = smem_base + L::BAR_OFF;
+    auto q_full = [&](int t) { return bars + 8 * t; };
+    auto q_empty = [&](int t) { return bars + 8 * (2 + t); };
+    auto k_full = [&](int s) { return bars + 8 * (4 + s); };
+    auto k_empty = [&](int s) { return bars + 8 * (4 + S + s); };
+    auto v_full = [&](int s) { return bars + 8 * (4 + 2 * S + s); };
+    auto v_empty = [&](int s) { return bars + 8 * (4 + 3 * S + s); };
+    auto s_full = [&](int t) { return bars + 8 * (4 + 4 * S + t); };
+    auto p_full = [&](int t) { return bars + 8 * (6 + 4 * S + t); };
+    auto o_final = [&](int t) { return bars + 8 * (8 + 4 * S + t); };
+    volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(smem_gen + L::TMEM_PTR_OFF);
+    constexpr uint32_t TMEM_COLS = 512;
+
+    if (warp == 1 && lane == 0) {
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+            mbar_init(q_full(t), 1); mbar_init(q_empty(t), 1); mbar_init(s_full(t), 1);
+            mbar_init(p_full(t), 128); mbar_init(o_final(t), 1);
+        }
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            mbar_init(k_full(s), 1); mbar_init(k_empty(s), 1); mbar_init(v_full(s), 1); mbar_init(v_empty(s), 1);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    } else if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_base + L::TMEM_PTR_OFF), "r"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    } else if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_q) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    if (warp < 4) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
+        if (warp == 0) {
+            // ===================================== TMA producer =====================================
+            if (lane == 0) {
+                const bool paged = p.block_tables != nullptr;
+                uint32_t kv_it = 0, q_use0 = 0, q_use1 = 0;
+                Unit u;
+                for (int w = blockIdx.x; get_unit(p, w, u); w += gridDim.x) {
+                    const int kvh = u.head / p.G;
+                    if (u.n_t0 > 0) {
+                        mbar_wait(q_empty(0), (q_use0 & 1u) ^ 1u);
+                        ++q_use0;
+                        mbar_expect_tx(q_full(0), TC_TILE_BYTES);
+                        tma_load_3d(sQ, &map_q, q_full(0), 0, u.head, u.q0 + u.m0);
+                        tma_load_3d(sQ + TC_HALF_BYTES, &map_q, q_full(0), 64, u.head, u.q0 + u.m0);
+                    }
+                    if (u.n_t1 > 0) {
+                        mbar_wait(q_empty(1), (q_use1 & 1u) ^ 1u);
+                        ++q_use1;
+                        mbar_expect_tx(q_full(1), TC_TILE_BYTES);
+                        tma_load_3d(sQ + TC_TILE_BYTES, &map_q, q_full(1), 0, u.head, u.q0 + u.m0 + TC_BM);
+                        tma_load_3d(sQ + TC_TILE_BYTES + TC_HALF_BYTES, &map_q, q_full(1), 64, u.head, u.q0 + u.m0 + TC_BM);
+                    }
+                    const int32_t* bt = paged ? p.block_tables + (int64_t)u.b * p.bt_row_stride : nullptr;
+                    for (int j = 0; j < u.n_max; ++j, ++kv_it) {
+                        const int n0 = j * TC_BN;
+                        const int row = paged ? __ldg(bt + n0 / B200_PAGE) * B200_PAGE + (n0 & (B200_PAGE - 1)) : u.k0 + n0;
+                        const uint32_t st = kv_it % S, par = (kv_it / S) & 1u;
+                        mbar_wait(k_empty(st), par ^ 1u);
+                        mbar_expect_tx(k_full(st), TC_TILE_BYTES);
+                        tma_load_3d(sK + st * TC_TILE_BYTES, &map_k, k_full(st), 0, kvh, row);
+                        tma_load_3d(sK + st * TC_TILE_BYTES + TC_HALF_BYTES, &map_k, k_full(st), 64, kvh, row);
+                        mbar_wait(v_empty(st), par ^ 1u);
+                        mbar_expect_tx(v_full(st), TC_TILE_BYTES);
+                        tma_load_3d(sV + st * TC_TILE_BYTES, &map_v, v_full(st), 0, kvh, row);
+                        tma_load_3d(sV + st * TC_TILE_BYTES + TC_HALF_BYTES, &map_v, v_full(st), 64, kvh, row);
+                    }
+                }
+            }
+        } else if (warp == 1) {
+            // ===================================== MMA issuer =======================================
+            if (lane == 0) {
+                constexpr uint32_t IDESC_QK = umma_idesc(0);           // B = K tile, K-major
+                constexpr uint32_t IDESC_PV = umma_idesc(1);           // B = V tile, MN-major
+                auto issue_qk = [&](int t, uint32_t st) {
+                    const uint32_t kst = sK + st * TC_TILE_BYTES, qst = sQ + t * TC_TILE_BYTES;
+                    const uint32_t d = tmem_base + t * 256;
+#pragma unroll
+                    for (int ks = 0; ks < 8; ++ks) {
+                        const uint32_t off = (ks >> 2) * TC_HALF_BYTES + (ks & 3) * 32;
+                        tc_mma_ss(d, umma_desc(qst + off, 0, 1024), umma_desc(kst + off, 0, 1024), IDESC_QK, ks > 0);
+                    }
+                };
+                auto issue_pv = [&](int t, uint32_t st, bool first) {
+                    const uint32_t vst = sV + st * TC_TILE_BYTES;
+                    const uint32_t d = tmem_base + t * 256 + 128, a = tmem_base + t * 256;
+#pragma unroll
+                    for (int kk = 0; kk < 8; ++kk)
+                        tc_mma_ts(d, a + kk * 8, umma_desc(vst + kk * 2048, TC_HALF_BYTES, 1024), IDESC_PV, (!first || kk > 0));
+                };
+                uint32_t kv_it = 0, q_use[2] = {0, 0}, p_cnt[2] = {0, 0};
+                Unit u;
+                for (int w = blockIdx.x; get_unit(p, w, u); w += gridDim.x) {
+#pragma unroll
+                    for (int t = 0; t < 2; ++t)
+                        if (u.nt(t) > 0) { mbar_wait(q_full(t), q_use[t] & 1u); ++q_use[t]; }
+                    if (u.n_max > 0) {
+                        const uint32_t st0 = kv_it % S;
+                        mbar_wait(k_full(st0), (kv_it / S) & 1u);
+                        tc_fence_after();
+#pragma unroll
+                        for (int t = 0; t < 2; ++t)
+                            if (u.nt(t) > 0) {
+                                issue_qk(t, st0);
+                                tc_commit(s_full(t));
+                                if (u.nt(t) == 1) tc_commit(q_empty(t));
+                            }
+                        tc_commit(k_empty(st0));
+                    }
+                    for (int j = 0; j < u.n_max; ++j) {
+                        const uint32_t it = kv_it + j, st = it % S, par = (it / S) & 1u;
+                        mbar_wait(v_full(st), par);
+                        if (j + 1 < u.n_max) mbar_wait(k_full((it + 1) % S), ((it + 1) / S) & 1u);
+                        tc_fence_after();
+#pragma unroll
+                        for (int t = 0; t < 2; ++t) {
+                            if (j < u.nt(t)) {
+                                mbar_wait(p_full(t), p_cnt[t] & 1u);
+                                ++p_cnt[t];
+                                tc_fence_after();
+                                issue_pv(t, st, j == 0);
+                                if (j + 1 < u.nt(t)) {
+                                    issue_qk(t, (it + 1) % S);
+                                    tc_commit(s_full(t));
+                                    if (j + 2 == u.nt(t)) tc_commit(q_empty(t));   // that was the last Q read
+                                } else {
+                                    tc_commit(o_final(t));
+                                }
+                            }
+                        }
+                        tc_commit(v_empty(st));
+                        if (j + 1 < u.n_max) tc_commit(k_empty((it + 1) % S));
+                    }
+                    kv_it += u.n_max;
+                }
+            }
+        }
+    } else {
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
+        // ======================== softmax + correction + epilogue warpgroups =====================
+        const int t = (warp - 4) >> 2;                              // query tile of this warpgroup
+        const int wq = warp & 3;                                    // TMEM lane quarter this warp may touch
+        const int row_in_tile = wq * 32 + lane;
+        const uint32_t lane_addr = (uint32_t)(wq * 32) << 16;
+        const uint32_t tS = tmem_base + t * 256 + lane_addr;
+        const uint32_t tO = tS + 128;
+        const uint64_t scale2 = pack2(p.scale_log2, p.scale_log2);
+        uint32_t s_cnt = 0, o_cnt = 0, kv_it = 0;
+        Unit u;
+        for (int w = blockIdx.x; get_unit(p, w, u); w += gridDim.x) {
+            const int nt = u.nt(t);
+            const int r_begin = u.m0 + t * TC_BM;
+            const int row = r_begin + row_in_tile;                  // query index within the sequence
+            const int offset = u.Lk - u.Lq;
+            float m_used = -INFINITY;                               // running maximum, scaled (log2) domain
+            uint64_t l2 = pack2(0.f, 0.f);                          // two partial row sums
+
+            for (int j = 0; j < nt; ++j) {
+                const int n0 = j * TC_BN;
+                mbar_wait(s_full(t), s_cnt & 1u);
+                ++s_cnt;
+                tc_fence_after();
+                uint32_t s[128];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&s[c * 32]));
+                tmem_wait_ld();
+                if ((n0 + TC_BN > u.Lk) || (n0 + TC_BN - 1 > r_begin + offset)) {      // tail or diagonal tile
+                    const int lim = min(u.Lk - 1, row + offset) - n0;                  // last visible column of this row
+#pragma unroll
+                    for (int i = 0; i < 128; ++i)
+                        if (i > lim) s[i] = 0xff800000u;                                // -inf
+                }
+                float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+                for (int i = 0; i < 128; i += 4) {
+                    mx0 = max3(mx0, __uint_as_float(s[i]), __uint_as_float(s[i + 1]));
+                    mx1 = max3(mx1, __uint_as_float(s[i + 2]), __uint_as_float(s[i + 3]));
+                }
+                const float mx = fmaxf(mx0, mx1) * p.scale_log2;
+                // lazy rescale: keep exponentiating against m_used until some row's max outgrows it by 2^8
+                const bool grow = mx > m_used + TC_RESCALE_THRESHOLD || (m_used == -INFINITY && mx > -INFINITY);
+                if (__any_sync(0xffffffffu, grow)) {
+                    const float m_new = fmaxf(m_used, mx);
+                    const float alpha = fast_exp2(m_used - (m_new == -INFINITY ? 0.f : m_new));   // 0 when m_used = -inf
+                    l2 = mul2(l2, pack2(alpha, alpha));
+                    m_used = m_new;
+                    if (j > 0) {                                    // PV(j-1) completed before s_full(j) fired
+                        const uint64_t a2 = pack2(alpha, alpha);
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {
+                            uint32_t o[32];
+                            tmem_ld32(tO + c * 32, o);
+                            tmem_wait_ld();
+#pragma unroll
+                            for (int i = 0; i < 32; i += 2) {
+                                float a, b;
+                                unpack2(mul2(pack2(__uint_as_float(o[i]), __uint_as_float(o[i + 1])), a2), a, b);
+                                o[i] = __float_as_uint(a); o[i + 1] = __float_as_uint(b);
+                            }
+                            tmem_st32(tO + c * 32, o);
+                        }
+                    }
+                }
+                const float neg_m = m_used == -INFINITY ? 0.f : -m_used;
+                const uint64_t negm2 = pack2(neg_m, neg_m);
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    uint32_t pk[16];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        float x0, x1;
+                        unpack2(fma2(pack2(__uint_as_float(s[c * 32 + 2 * i]), __uint_as_float(s[c * 32 + 2 * i + 1])), scale2, negm2), x0, x1);
+                        const float p0 = fast_exp2(x0), p1 = fast_exp2(x1);
+                        l2 = add2(l2, pack2(p0, p1));
+                        pk[i] = cvt_bf16x2(p0, p1);
+                    }
+                    tmem_st16(tS + c * 16, pk);                     // P over the first 64 columns of S
+                }
+                tmem_wait_st();
+                if (n0 + TC_BN > u.Lk) {
+                    // Rows of the V tile past the context may hold NaN garbage (torch.empty cache):
+                    // 0 * NaN would poison O, so zero them in shared memory before PV reads them.
+                    const uint32_t it = kv_it + j, st = it % S;
+                    mbar_wait(v_full(st), (it / S) & 1u);
+                    uint8_t* vt = smem_gen + L::V_OFF + st * TC_TILE_BYTES;
+                    const int first = u.Lk - n0;                    // first invalid row of this tile
+                    for (int idx = row_in_tile; idx < (TC_BN - first) * 16; idx += 128) {
+                        const int r = first + (idx >> 4), c16 = idx & 15;
+                        *reinterpret_cast<int4*>(vt + (c16 >> 3) * TC_HALF_BYTES + r * 128 + (c16 & 7) * 16) = make_int4(0, 0, 0, 0);
+                    }
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                }
+                tc_fence_before();
+                mbar_arrive(p_full(t));
+            }
+            kv_it += u.n_max;
+
+            // ---- epilogue: O / l -> bf16 -> global (rows beyond the sequence are dropped) --------
+            if (nt > 0) {
+                mbar_wait(o_final(t), o_cnt & 1u);
+                ++o_cnt;
+                tc_fence_after();
+                float la, lb;
+                unpack2(l2, la, lb);
+                const float l_sum = la + lb;
+                const float inv = l_sum > 0.f ? 1.f / l_sum : 0.f;
+                __nv_bfloat16* orow = p.out + (int64_t)(u.q0 + row) * p.out_token_stride + (int64_t)u.head * B200_HD;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    uint32_t o[32];
+                    tmem_ld32(tO + c * 32, o);
+                    tmem_wait_ld();
+                    if (row < u.Lq) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            int4 v;
+                            v.x = (int)cvt_bf16x2(__uint_as_float(o[8 * i + 0]) * inv, __uint_as_float(o[8 * i + 1]) * inv);
+                            v.y = (int)cvt_bf16x2(__uint_as_float(o[8 * i + 2]) * inv, __uint_as_float(o[8 * i + 3]) * inv);
+                            v.z = (int)cvt_bf16x2(__uint_as_float(o[8 * i + 4]) * inv, __uint_as_float(o[8 * i + 5]) * inv);
+                            v.w = (int)cvt_bf16x2(__uint_as_float(o[8 * i + 6]) * inv, __uint_as_float(o[8 * i + 7]) * inv);
+                            *reinterpret_cast<int4*>(orow + c * 32 + i * 8) = v;
+                        }
+                    }
+                }
+                // O(t) is overwritten by the next unit's first PV, which waits on this warpgroup's
+                // next p_full arrival (program order) => the reads above are complete by then.
+                tc_fence_before();
+            }
+        }
+    }
+
+    // ---- teardown --------------------------------------------------------------------------------
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+    }
+}
+
+int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32_t max_items, cudaStream_t stream) {
+    if (a.batch == 0 || a.total_q == 0 || a.max_q == 0) return 0;
+    if (get_encode_fn() == nullptr) return -6;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(prefill_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PsSmem::ALLOC);
+        if (e != cudaSuccess) return (int)e;
+        attr_set = true;
+    }
+    CUtensorMap mq, mk, mv;
+    const bool paged = a.block_tables != nullptr;
+    if (!make_map(&mq, a.q, (uint64_t)a.total_q, (uint64_t)a.Hq, (uint64_t)a.q_token_stride)) return -6;
+    if (paged) {
+        const uint64_t rows = (uint64_t)a.num_cache_blocks * B200_PAGE;
+        if (!make_map(&mk, a.k, rows, (uint64_t)a.Hkv, (uint64_t)a.Hkv * B200_HD)) return -6;
+        if (!make_map(&mv, a.v, rows, (uint64_t)a.Hkv, (uint64_t)a.Hkv * B200_HD)) return -6;
+    } else {
+        if (!make_map(&mk, a.k, (uint64_t)a.total_q, (uint64_t)a.Hkv, (uint64_t)a.k_token_stride)) return -6;
+        if (!make_map(&mv, a.v, (uint64_t)a.total_q, (uint64_t)a.Hkv, (uint64_t)a.v_token_stride)) return -6;
+    }
+    PersistParams p;
+    p.cu_q = a.cu_q; p.cu_k = a.cu_k; p.block_tables = a.block_tables; p.bt_row_stride = a.bt_row_stride;
+    p.out = (__nv_bfloat16*)a.out; p.out_token_stride = a.out_token_stride;
+    p.Hq = a.Hq; p.G = a.Hq / a.Hkv; p.scale_log2 = a.scale * 1.4426950408889634f;
+    p.plan = plan; p.items = plan + PLAN_HEADER_WORDS + a.batch;
+    int64_t units = (int64_t)max_items * a.Hq;
+    int grid = sm_count();
+    if (units < grid) grid = (int)units;
+    if (grid < 1) grid = 1;
+    prefill_persist_kernel<<<grid, 384, PsSmem::ALLOC, stream>>>(mq, mk, mv, p);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace b200

@@ -31,6 +31,9 @@ struct DecodeArgs {
     const int32_t* context_lens; const int32_t* block_tables; int32_t bt_row_stride;
     int32_t batch, Hq, Hkv; float scale; int32_t num_splits;
     float* ws_o; float* ws_lse;
+    // varlen form: non-null => rows are row_list[0 .. *n_rows), lengths/tokens from cu_k / cu_q
+    const int32_t* cu_q = nullptr; const int32_t* cu_k = nullptr;
+    const int32_t* row_list = nullptr; const int32_t* n_rows = nullptr;
 };
 int launch_attn_decode(const DecodeArgs& a, cudaStream_t stream);
 
@@ -45,5 +48,19 @@ int launch_attn_prefill_mma(const PrefillArgs& a, cudaStream_t stream);
 int launch_attn_prefill_tc(const PrefillArgs& a, cudaStream_t stream);   // tcgen05/TMEM/TMA, 2 query tiles in flight
 int launch_attn_prefill_tc1(const PrefillArgs& a, cudaStream_t stream);  // same, 1 query tile (bring-up / small shapes)
 bool prefill_tc_available();
+
+// ---- step plan (attn_plan.cu) + persistent tcgen05 prefill (attn_prefill_persist.cu) ----------
+// plan buffer, int32 words: [0] n_items  [1] n_decode_rows  [2..15] reserved
+//                           [16 .. 16 + batch)        rows with exactly one query token
+//                           [.. + 2*max_items)        (sequence, 256-row tile) pairs, heaviest first
+constexpr int PLAN_HEADER_WORDS = 16;
+constexpr int PLAN_TILE_ROWS = 256;
+inline int32_t plan_max_items(int32_t batch, int32_t total_q) { return total_q / PLAN_TILE_ROWS + batch; }
+inline size_t plan_bytes(int32_t batch, int32_t total_q) {
+    return ((size_t)PLAN_HEADER_WORDS + 2 * (size_t)plan_max_items(batch, total_q) + (size_t)batch) * sizeof(int32_t);
+}
+int launch_attn_plan(const int32_t* cu_q, const int32_t* cu_k, int32_t batch, int32_t route_decode,
+                     int32_t* plan, int32_t max_items, cudaStream_t stream);
+int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32_t max_items, cudaStream_t stream);
 
 }  // namespace b200

@@ -213,6 +213,69 @@ def test_prefill_long_causal_row_sampled_vs_oracle(ops, variant):
     assert maxerr(got, want) <= ATOL
 
 
+# ---------------------------------------------------------------------------- planned (persistent) path
+@pytest.mark.parametrize("Hq,Hkv", [(16, 8), (4, 1), (5, 1), (32, 8)])
+def test_planned_paged_mixed_vs_oracle(ops, Hq, Hkv):
+    """Step plan: multi-token rows -> persistent tcgen05 kernel, single-token rows -> decode kernel."""
+    lens_k = [700, 129, 128, 1, 257, 513, 64, 1000, 300, 2, 1025]
+    lens_q = [188, 1, 128, 1, 1, 257, 64, 40, 300, 2, 513]
+    c = make_paged_case(61 + Hq, lens_q, lens_k, Hq, Hkv, pad=-1)
+    want = oracle.attn_varlen(c["q"], c["k_cache"], c["v_cache"], c["cu_seqlens_q"], c["cu_seqlens_k"], SCALE,
+                              c["block_tables"])
+    cu_q, cu_k = dev(c["cu_seqlens_q"]), dev(c["cu_seqlens_k"])
+    plan = ops.attn_plan(cu_q, cu_k, sum(lens_q), route_decode=True)
+    n_items, n_dec = plan.counts()
+    assert n_dec == sum(1 for x in lens_q if x == 1)
+    assert n_items == sum((x + 255) // 256 for x in lens_q if x > 1)
+    got = torch.full_like(dev(c["q"]), float("nan"))
+    for _ in range(2):                                       # the same plan serves every layer of a step
+        ops.attn_varlen_planned(dev(c["q"]), dev(c["k_cache"]), dev(c["v_cache"]), cu_q, cu_k, c["max_seqlen_q"],
+                                c["max_seqlen_k"], SCALE, block_table=dev(c["block_tables"]), plan=plan, out=got)
+    assert torch.isfinite(got.float()).all()
+    assert maxerr(got, want) <= ATOL
+
+
+@pytest.mark.parametrize("Hq,Hkv", [(16, 8), (8, 1)])
+def test_planned_unpaged_vs_oracle(ops, Hq, Hkv):
+    lens = [128, 1, 63, 64, 65, 300, 7, 1, 600]
+    g = torch.Generator().manual_seed(9)
+    T, D = sum(lens), 128
+    qkv = torch.randn(T, (Hq + 2 * Hkv) * D, generator=g).bfloat16()
+    q = qkv[:, :Hq * D].reshape(T, Hq, D).contiguous()
+    k = qkv[:, Hq * D:(Hq + Hkv) * D].reshape(T, Hkv, D).contiguous()
+    v = qkv[:, (Hq + Hkv) * D:].view(T, Hkv, D)
+    cu = torch.tensor([0] + torch.tensor(lens).cumsum(0).tolist(), dtype=torch.int32)
+    want = oracle.attn_varlen(q, k, v, cu, cu, SCALE)
+    qkv_d = qkv.cuda()
+    got = ops.attn_varlen_planned(q.cuda(), k.cuda(), qkv_d[:, (Hq + Hkv) * D:].view(T, Hkv, D), cu.cuda(), cu.cuda(),
+                                  max(lens), max(lens), SCALE)
+    assert maxerr(got, want) <= ATOL
+
+
+def test_planned_long_causal_and_many_units(ops):
+    """More work units than SMs (persistent loop, barrier phases across units) + a long causal row."""
+    lens = [4160] + [300] * 40 + [1] * 30
+    c = make_paged_case(78, lens, lens, 8, 1)
+    want = oracle.attn_varlen(c["q"], c["k_cache"], c["v_cache"], c["cu_seqlens_q"], c["cu_seqlens_k"], SCALE,
+                              c["block_tables"])
+    got = ops.attn_varlen_planned(dev(c["q"]), dev(c["k_cache"]), dev(c["v_cache"]), dev(c["cu_seqlens_q"]),
+                                  dev(c["cu_seqlens_k"]), max(lens), max(lens), SCALE, block_table=dev(c["block_tables"]))
+    assert maxerr(got, want) <= ATOL
+
+
+def test_planned_chunked_prefix_rows(ops):
+    """Chunked prefill over a long cached prefix: Lq << Lk, bottom-right causal offset, ragged tails."""
+    lens_q = [64, 64, 200, 513, 1, 31]
+    lens_k = [2112, 2111, 1224, 1537, 2048, 31]
+    c = make_paged_case(79, lens_q, lens_k, 8, 2)
+    want = oracle.attn_varlen(c["q"], c["k_cache"], c["v_cache"], c["cu_seqlens_q"], c["cu_seqlens_k"], SCALE,
+                              c["block_tables"])
+    kc, vc = dev(c["k_cache"]), dev(c["v_cache"])
+    got = ops.attn_varlen_planned(dev(c["q"]), kc, vc, dev(c["cu_seqlens_q"]), dev(c["cu_seqlens_k"]), max(lens_q),
+                                  max(lens_k), SCALE, block_table=dev(c["block_tables"]))
+    assert maxerr(got, want) <= ATOL
+
+
 # ---------------------------------------------------------------------------- Attention.forward
 def test_attention_forward_prefix_sharing_same_step(ops):
     """a branch scheduled in the same step reads prefix blocks that another sequence

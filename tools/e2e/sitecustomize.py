@@ -4,8 +4,12 @@ gets the same harness patches, applied identically to BOTH arms (reference and d
 
   B200E2E_RANDOM_INIT=<seed>  replace `load_model` (no checkpoints offline) by a seeded
                               N(0, 0.02) init of every parameter, norm weights = 1
-  B200E2E_GREEDY=1            replace Sampler.forward by argmax and record the top-2 logit margin
-                              of every decision (the reference's sampler forbids greedy, F12)
+  B200E2E_GREEDY=1            replace Sampler.forward by argmax and record (step, argmax, top-2 logit
+                              margin) of every decision per seq_id (the reference's sampler forbids
+                              greedy, F12)
+  B200E2E_FORCE_TOKENS=<json> with GREEDY: still record this arm's own argmax, but FEED the token ids
+                              of the other arm's run (teacher forcing), so every decision of the two
+                              arms is taken on an identical context
   B200E2E_SHM_BYTES=<n>       size of the rank-0 -> worker shared-memory mailbox (F11)
 
 and then chains to the product hook nano-vllm-v1_b200/dropin/sitecustomize.py (B200ATTN_DROPIN)."""
@@ -40,24 +44,43 @@ def _patch(module):
         module.load_model = seeded_init
     if _GREEDY:
         sampler = importlib.import_module("nanovllm.layers.sampler")
+        ctx_mod = importlib.import_module("nanovllm.utils.context")
+        forced = None
+        if os.environ.get("B200E2E_FORCE_TOKENS"):                    # teacher forcing: feed the other arm's tokens
+            with open(os.environ["B200E2E_FORCE_TOKENS"]) as f:
+                forced = json.load(f)["token_ids"]
+        cur = {}
 
         def greedy(self, logits, temperatures):
             top2 = torch.topk(logits.float(), 2, dim=-1)
-            _MARGINS.append((top2.values[:, 0] - top2.values[:, 1]).cpu())
-            return top2.indices[:, 0]
+            choice = top2.indices[:, 0]
+            margins = (top2.values[:, 0] - top2.values[:, 1]).tolist()
+            picks = choice.tolist()
+            seqs = cur.get("seqs")
+            if seqs is not None:
+                need = ctx_mod.get_context().seq_need_compute_logits
+                rows = need.tolist() if need is not None and need.numel() else list(range(len(seqs)))
+                out = list(picks)
+                for row, si in enumerate(rows):
+                    sq = seqs[si]
+                    sid = int(getattr(sq, "seq_id", -1))
+                    step = len(sq) - sq.num_prompt_tokens
+                    _PER_SEQ.setdefault(sid, []).append((step, picks[row], margins[row]))
+                    k = sid - int(os.environ.get("B200E2E_FIRST_SEQ_ID", "1"))   # earlier ids: warm-up sequences
+                    if forced is not None and 0 <= k < len(forced) and step < len(forced[k]):
+                        out[row] = forced[k][step]
+                if forced is not None:
+                    return torch.tensor(out, dtype=choice.dtype, device=choice.device)
+            return choice
         sampler.Sampler.forward = greedy
         orig_run = module.ModelRunner.run
 
         def run(self, seqs):
-            n0 = len(_MARGINS)
-            result = orig_run(self, seqs)
-            if self.rank == 0 and len(_MARGINS) > n0:                 # attribute this step's margins to seq ids
-                _, need = result
-                rows = need.tolist() if need.numel() else list(range(len(seqs)))
-                m = _MARGINS[-1].tolist()
-                for row, si in enumerate(rows):
-                    _PER_SEQ.setdefault(int(getattr(seqs[si], "seq_id", -1)), []).append(m[row])
-            return result
+            cur["seqs"] = seqs if self.rank == 0 else None
+            try:
+                return orig_run(self, seqs)
+            finally:
+                cur["seqs"] = None
         module.ModelRunner.run = run
         out = os.environ.get("B200E2E_MARGINS_OUT")
         if out:

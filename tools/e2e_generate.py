@@ -37,6 +37,8 @@ def launcher(a):
     if a.greedy:
         env["B200E2E_GREEDY"] = "1"
         env["B200E2E_MARGINS_OUT"] = a.out + ".margins"
+        if a.force_tokens:
+            env["B200E2E_FORCE_TOKENS"] = os.path.abspath(a.force_tokens)
     cmd = [sys.executable, os.path.abspath(__file__), "--worker"] + [x for x in sys.argv[1:] if x != "--worker"]
     return subprocess.run(cmd, env=env).returncode
 
@@ -60,53 +62,71 @@ def worker(a):
     sp = SamplingParams(temperature=0.6, ignore_eos=True, max_tokens=a.out_len)
     llm.generate([[1, 2, 3]], SamplingParams(temperature=0.6, ignore_eos=True, max_tokens=4), use_tqdm=False)   # warm-up, bench.py:22
     torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    outs = llm.generate(prompts, sp, use_tqdm=False)
-    torch.cuda.synchronize()
-    dt = time.perf_counter() - t0
+    from nanovllm.engine.sequence import Sequence
+    first_id = next(Sequence.counter) + 1                                  # ids below belong to warm-up sequences
+    os.environ["B200E2E_FIRST_SEQ_ID"] = str(first_id)
+    times = []
+    for _ in range(max(a.repeat, 1)):                                      # first pass includes torch.compile re-traces
+        t0 = time.perf_counter()
+        outs = llm.generate(prompts, sp, use_tqdm=False)
+        torch.cuda.synchronize()
+        times.append(time.perf_counter() - t0)
+        if a.greedy:
+            break                                                          # recorded decisions must be those of ONE pass
+    dt = min(times)
     import b200attn.install as dropin_mod
     n_out = sum(len(o["token_ids"]) for o in outs)
     rec = dict(arm=a.arm, size=a.size, layers=a.layers, tp=a.tp, num_seqs=a.num_seqs, in_len=a.in_len, out_len=a.out_len,
                shared_prefix=a.shared_prefix, chunked_prefill=a.chunked_prefill, enforce_eager=a.enforce_eager,
-               greedy=a.greedy, seconds=dt, init_seconds=t_init, generated_tokens=n_out, tok_per_s=n_out / dt,
+               greedy=a.greedy, seconds=dt, init_seconds=t_init, generated_tokens=n_out, tok_per_s=n_out / dt, seconds_all=times, first_seq_id=first_id,
                total_tok_per_s=(n_out + sum(len(p) for p in prompts)) / dt, dropin_installed=dropin_mod.installed(),
                gpu=torch.cuda.get_device_name(0), token_ids=[o["token_ids"] for o in outs] if a.greedy else None)
     os.makedirs(os.path.dirname(os.path.abspath(a.out)), exist_ok=True)
     with open(a.out, "w") as f:
         json.dump(rec, f)
     print(json.dumps({k: v for k, v in rec.items() if k != "token_ids"}), flush=True)
-    llm.exit() if hasattr(llm, "exit") else None
     return 0
 
 
 def compare(ref_path, our_path, steps, tie_margin):
-    """Greedy parity: token ids must be identical for `steps` decisions per sequence; a sequence may
-    diverge only at a decision whose reference top-2 logit margin is below `tie_margin` (a near-tie
-    that bf16 rounding legitimately flips).  Prints a JSON verdict; exit 1 on a real mismatch."""
+    """Greedy parity over `steps` decisions per sequence.  `our_path` is a TEACHER-FORCED run (it was fed
+    the reference's tokens), so every decision of both arms was taken on an identical context: the
+    arg-max token ids must be identical, except where the top-2 logit margin is within `tie_margin`
+    (bf16 logits: one ulp at |x| in [2,4) is 0.0156) -- a tie that rounding legitimately flips.
+    Prints a JSON verdict; exit status 1 if any decision differs outside a near-tie."""
     ref, our = json.load(open(ref_path)), json.load(open(our_path))
-    per_seq = json.load(open(ref_path + ".margins"))                      # seq_id -> margins of its decisions
-    ids = sorted(int(k) for k in per_seq)[-len(ref["token_ids"]):]        # earlier ids belong to the warm-up generate
+    mref = json.load(open(ref_path + ".margins"))
+    mour = json.load(open(our_path + ".margins"))
     n = len(ref["token_ids"])
-    identical, tie_div, real_div, detail = 0, 0, 0, []
-    all_margins = []
+    total = same = tie = real = 0
+    seq_identical = 0
+    worst, margins = [], []
     for i in range(n):
-        a, b = ref["token_ids"][i][:steps], our["token_ids"][i][:steps]
-        m = per_seq[str(ids[i])][:steps]
-        all_margins.extend(m)
-        if a == b:
-            identical += 1
-            continue
-        j = next(k for k in range(min(len(a), len(b))) if a[k] != b[k])
-        is_tie = m[j] < tie_margin
-        tie_div += is_tie
-        real_div += not is_tie
-        detail.append(dict(seq=i, step=j, ref_margin=round(m[j], 5)))
-    all_margins.sort()
-    verdict = dict(sequences=n, steps=steps, identical=identical, diverged_at_near_tie=tie_div, diverged_for_real=real_div,
-                   tie_margin=tie_margin, first_divergences=detail[:16],
-                   margin_quantiles=dict(p0=all_margins[0], p1=all_margins[len(all_margins) // 100],
-                                         p50=all_margins[len(all_margins) // 2]) if all_margins else None,
-                   ref_tok_per_s=ref.get("tok_per_s"), ours_tok_per_s=our.get("tok_per_s"))
+        r = {st: (tok, mg) for st, tok, mg in mref[str(i + ref["first_seq_id"])]}
+        o = {st: (tok, mg) for st, tok, mg in mour[str(i + our["first_seq_id"])]}
+        ok_seq = True
+        for st in range(steps):
+            if st not in r or st not in o:
+                continue
+            total += 1
+            margins.append(r[st][1])
+            if r[st][0] == o[st][0]:
+                same += 1
+                continue
+            ok_seq = False
+            if min(r[st][1], o[st][1]) <= tie_margin:
+                tie += 1
+            else:
+                real += 1
+            worst.append(dict(seq=i, step=st, ref_margin=round(r[st][1], 5), our_margin=round(o[st][1], 5)))
+        seq_identical += ok_seq
+    margins.sort()
+    worst.sort(key=lambda d: -min(d["ref_margin"], d["our_margin"]))
+    verdict = dict(sequences=n, steps=steps, decisions=total, identical=same, differ_at_near_tie=tie, differ_for_real=real,
+                   sequences_fully_identical=seq_identical, tie_margin=tie_margin, largest_margin_differences=worst[:8],
+                   ref_margin_quantiles=dict(p0=margins[0], p1=margins[len(margins) // 100], p10=margins[len(margins) // 10],
+                                             p50=margins[len(margins) // 2]) if margins else None,
+                   teacher_forced=True)
     print(json.dumps(verdict))
     return verdict
 
@@ -133,14 +153,16 @@ def main():
     ap.add_argument("--worker", action="store_true")
     ap.add_argument("--compare", nargs=2)
     ap.add_argument("--steps", type=int, default=64)
-    ap.add_argument("--tie-margin", type=float, default=0.05)
+    ap.add_argument("--tie-margin", type=float, default=0.032, help="2 bf16 ulps at |logit| in [2,4)")
+    ap.add_argument("--force-tokens", default=None, help="JSON of the other arm's greedy run to teacher-force")
+    ap.add_argument("--repeat", type=int, default=2)
     a = ap.parse_args()
     if a.compare:
         v = compare(a.compare[0], a.compare[1], a.steps, a.tie_margin)
         if a.out:
             with open(a.out, "w") as f:
                 json.dump(v, f)
-        return 1 if v["diverged_for_real"] else 0
+        return 1 if v["differ_for_real"] else 0
     return worker(a) if a.worker else launcher(a)
 
 

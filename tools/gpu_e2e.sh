@@ -4,10 +4,11 @@
 TAG=${1:-e2e}; shift
 mkdir -p gpurun_out
 COMMON="--size 0.6b --num-seqs 256 --in-len 128 --out-len 256 --chunked-prefill $@"
-for arm in reference dropin; do
-  timeout 900 python tools/e2e_generate.py --arm $arm $COMMON --greedy --out gpurun_out/${TAG}_${arm}_greedy.json > gpurun_out/${TAG}_${arm}_greedy.log 2>&1
-  echo "$arm greedy exit $?"; tail -n 2 gpurun_out/${TAG}_${arm}_greedy.log | cut -c1-600
-done
+timeout 900 python tools/e2e_generate.py --arm reference $COMMON --greedy --out gpurun_out/${TAG}_reference_greedy.json > gpurun_out/${TAG}_reference_greedy.log 2>&1
+echo "reference greedy exit $?"; tail -n 1 gpurun_out/${TAG}_reference_greedy.log | cut -c1-400
+# drop-in arm is teacher-forced with the reference's tokens: every decision is compared on an identical context
+timeout 900 python tools/e2e_generate.py --arm dropin $COMMON --greedy --force-tokens gpurun_out/${TAG}_reference_greedy.json --out gpurun_out/${TAG}_dropin_greedy.json > gpurun_out/${TAG}_dropin_greedy.log 2>&1
+echo "dropin greedy (teacher-forced) exit $?"; tail -n 1 gpurun_out/${TAG}_dropin_greedy.log | cut -c1-400
 python tools/e2e_generate.py --compare gpurun_out/${TAG}_reference_greedy.json gpurun_out/${TAG}_dropin_greedy.json --out gpurun_out/${TAG}_parity.json
 for arm in reference dropin; do
   timeout 900 python tools/e2e_generate.py --arm $arm $COMMON --out gpurun_out/${TAG}_${arm}.json > gpurun_out/${TAG}_${arm}.log 2>&1
