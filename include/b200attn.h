@@ -114,12 +114,14 @@ int b200_attn_prefill(const void* q, int64_t q_token_stride,
  *       rows with q_len > 1  -> persistent tcgen05 prefill kernel (work list sorted heaviest-first),
  *       rows with q_len == 1 -> split-K decode kernel (only when a block table exists),
  *     and is reused by every layer of the step.  No host reads, graph-capturable.
- *     plan: b200_attn_plan_bytes(batch, total_q) bytes of device memory, 16-byte aligned.
+ *     plan: b200_attn_plan_bytes(batch, total_q) bytes of device memory, 16-byte aligned; it is built for
+ *     one (num_heads, num_kv_heads) pair (the query-tile height depends on the GQA group being even).
  *     b200_attn_prefill_planned / b200_attn_decode_varlen write disjoint rows of `out`.
  */
 size_t b200_attn_plan_bytes(int32_t batch, int32_t total_q);
 int b200_attn_plan(const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k, int32_t batch, int32_t total_q,
-                   int32_t route_decode, void* plan, size_t plan_bytes, void* stream);
+                   int32_t num_heads, int32_t num_kv_heads, int32_t route_decode,
+                   void* plan, size_t plan_bytes, void* stream);
 int b200_attn_prefill_planned(const void* q, int64_t q_token_stride,
                               const void* k, const void* v,
                               int64_t k_token_stride, int64_t v_token_stride,

@@ -23,7 +23,7 @@ SIGNATURES = {
                                     c_void_p, c_void_p, c_void_p, c_int32, c_int32, c_int32, c_int32, c_int32,
                                     c_int32, c_int32, c_int32, c_int32, c_int64, c_float, c_int32, c_void_p]),
     "b200_attn_plan_bytes": (c_size_t, [c_int32, c_int32]),
-    "b200_attn_plan": (c_int32, [c_void_p, c_void_p, c_int32, c_int32, c_int32, c_void_p, c_size_t, c_void_p]),
+    "b200_attn_plan": (c_int32, [c_void_p, c_void_p, c_int32, c_int32, c_int32, c_int32, c_int32, c_void_p, c_size_t, c_void_p]),
     "b200_attn_prefill_planned": (c_int32, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_int64,
                                             c_void_p, c_void_p, c_void_p, c_int32, c_int32, c_int32, c_int32, c_int32,
                                             c_int32, c_int32, c_int32, c_int32, c_int64, c_float, c_void_p, c_size_t, c_void_p]),

@@ -73,8 +73,8 @@ class Attention(nn.Module):
                                    block_table=context.block_tables, variant=_PREFILL_VARIANT)
         plan = getattr(context, "_b200_plan", None)
         if plan is None or plan.total_q != q.shape[0]:
-            plan = ops.attn_plan(context.cu_seqlens_q, context.cu_seqlens_k, q.shape[0],
-                                 route_decode=context.block_tables is not None)
+            plan = ops.attn_plan(context.cu_seqlens_q, context.cu_seqlens_k, q.shape[0], self.num_heads,
+                                 self.num_kv_heads, route_decode=context.block_tables is not None)
             try:
                 context._b200_plan = plan                     # every layer of this step reuses it
             except AttributeError:

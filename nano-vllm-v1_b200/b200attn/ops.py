@@ -170,8 +170,8 @@ class StepPlan:
     prefill kernel + list of single-token rows for the decode kernel.  Built once per engine step
     and shared by every layer (the Context it is derived from is the same for all layers)."""
 
-    def __init__(self, buf: torch.Tensor, batch: int, total_q: int, route_decode: bool) -> None:
-        self.buf, self.batch, self.total_q, self.route_decode = buf, batch, total_q, route_decode
+    def __init__(self, buf: torch.Tensor, batch: int, total_q: int, route_decode: bool, heads) -> None:
+        self.buf, self.batch, self.total_q, self.route_decode, self.heads = buf, batch, total_q, route_decode, heads
 
     def counts(self):
         """(prefill work items, decode rows) -- synchronises; for tests and tools only."""
@@ -179,16 +179,17 @@ class StepPlan:
         return int(head[0]), int(head[1])
 
 
-def attn_plan(cu_seqlens_q: torch.Tensor, cu_seqlens_k: torch.Tensor, total_q: int, route_decode: bool) -> StepPlan:
+def attn_plan(cu_seqlens_q: torch.Tensor, cu_seqlens_k: torch.Tensor, total_q: int, num_heads: int, num_kv_heads: int,
+              route_decode: bool) -> StepPlan:
     _need_i32(cu_seqlens_q, "cu_seqlens_q")
     _need_i32(cu_seqlens_k, "cu_seqlens_k")
     B = cu_seqlens_q.numel() - 1
     lib = load_library()
     nbytes = lib.b200_attn_plan_bytes(max(B, 1), total_q)
     buf = torch.empty(nbytes, dtype=torch.uint8, device=cu_seqlens_q.device)
-    check(lib.b200_attn_plan(cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr(), B, total_q, 1 if route_decode else 0,
-                             buf.data_ptr(), nbytes, _stream()), "b200_attn_plan")
-    return StepPlan(buf, B, total_q, route_decode)
+    check(lib.b200_attn_plan(cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr(), B, total_q, num_heads, num_kv_heads,
+                             1 if route_decode else 0, buf.data_ptr(), nbytes, _stream()), "b200_attn_plan")
+    return StepPlan(buf, B, total_q, route_decode, (num_heads, num_kv_heads))
 
 
 def attn_varlen_planned(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens_q: torch.Tensor,
@@ -204,9 +205,6 @@ def attn_varlen_planned(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_se
     assert q.stride(-1) == 1 and q.stride(1) == D
     B = cu_seqlens_q.numel() - 1
     paged = block_table is not None
-    if plan is None:
-        plan = attn_plan(cu_seqlens_q, cu_seqlens_k, T, route_decode=paged)
-    assert plan.batch == B and plan.total_q == T and (not plan.route_decode or paged)
     if paged:
         _need_i32(block_table, "block_table")
         assert k.dim() == 4 and k.is_contiguous() and v.is_contiguous() and k.shape[1] == PAGE
@@ -217,6 +215,9 @@ def attn_varlen_planned(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_se
         assert k.dim() == 3 and k.stride(-1) == 1 and v.stride(-1) == 1 and k.stride(1) == D and v.stride(1) == D
         Hkv, ks, vs, nblocks = k.shape[1], k.stride(0), v.stride(0), 0
         bt_ptr, bt_stride = None, 0
+    if plan is None:
+        plan = attn_plan(cu_seqlens_q, cu_seqlens_k, T, Hq, Hkv, route_decode=paged)
+    assert plan.batch == B and plan.total_q == T and (not plan.route_decode or paged) and plan.heads == (Hq, Hkv)
     if out is None:
         out = torch.empty((T, Hq, D), dtype=q.dtype, device=q.device)
     lib = load_library()

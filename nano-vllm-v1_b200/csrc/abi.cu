@@ -165,12 +165,15 @@ size_t b200_attn_plan_bytes(int32_t batch, int32_t total_q) {
 }
 
 int b200_attn_plan(const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k, int32_t batch, int32_t total_q,
-                   int32_t route_decode, void* plan, size_t plan_bytes_given, void* stream) {
+                   int32_t num_heads, int32_t num_kv_heads, int32_t route_decode,
+                   void* plan, size_t plan_bytes_given, void* stream) {
     if (batch < 0 || total_q < 0) return B200_ERR_RANGE;
+    if (num_kv_heads <= 0 || num_heads <= 0 || num_heads % num_kv_heads != 0) return B200_ERR_SHAPE;
     if (!cu_seqlens_q || !cu_seqlens_k || !plan) return B200_ERR_NULL;
     if (!aligned16(plan)) return B200_ERR_ALIGN;
     if (plan_bytes_given < plan_bytes(batch > 0 ? batch : 1, total_q)) return B200_ERR_WORKSPACE;
-    return launch_attn_plan(cu_seqlens_q, cu_seqlens_k, batch, route_decode ? 1 : 0, (int32_t*)plan,
+    return launch_attn_plan(cu_seqlens_q, cu_seqlens_k, batch, route_decode ? 1 : 0,
+                            plan_tile_rows(num_heads, num_kv_heads), (int32_t*)plan,
                             plan_max_items(batch, total_q), (cudaStream_t)stream);
 }
 

@@ -2,8 +2,8 @@
 //
 // One tiny kernel, run ONCE per engine step (every layer of the step reuses its output), turns
 // cu_seqlens_q/k into
-//   * a work list for the persistent tcgen05 prefill kernel: one item per 256-row query tile
-//     of a sequence with q_len > 1 (or every sequence when routing is off), ordered by
+//   * a work list for the persistent tcgen05 prefill kernel: one item per query tile (128 rows when the
+//     kernel pairs two q heads of a GQA group per CTA, else 256 rows) of a sequence with q_len > 1 (or every sequence when routing is off), ordered by
 //     descending number of KV tiles (longest-processing-time-first for the static round-robin
 //     over the persistent CTAs);
 //   * the list of rows with exactly one query token, which go to the split-K decode kernel
@@ -18,21 +18,22 @@
 namespace b200 {
 
 constexpr int PLAN_THREADS = 1024;
-constexpr int PLAN_MAX_KEY = 2047;
+constexpr int PLAN_MAX_KEY = PLAN_THREADS - 1;          // one histogram bin per thread (40,960-token context = 320 tiles)
 
 __global__ void __launch_bounds__(PLAN_THREADS) attn_plan_kernel(
     const int32_t* __restrict__ cu_q, const int32_t* __restrict__ cu_k, int32_t batch, int32_t route_decode,
-    int32_t* __restrict__ plan, int32_t max_items) {
+    int32_t tile_rows, int32_t* __restrict__ plan, int32_t max_items) {
     __shared__ int32_t hist[PLAN_MAX_KEY + 1];
     __shared__ int32_t n_decode;
+    __shared__ int32_t warp_tot[PLAN_THREADS / 32];
     for (int i = threadIdx.x; i <= PLAN_MAX_KEY; i += PLAN_THREADS) hist[i] = 0;
     if (threadIdx.x == 0) n_decode = 0;
     __syncthreads();
     int32_t* decode_rows = plan + PLAN_HEADER_WORDS;
     int32_t* items = decode_rows + batch;
 
-    auto key_of = [](int mt, int Lq, int Lk) {
-        const int kv_end = min(Lk, (mt + 1) * PLAN_TILE_ROWS + (Lk - Lq));
+    auto key_of = [tile_rows](int mt, int Lq, int Lk) {
+        const int kv_end = min(Lk, (mt + 1) * tile_rows + (Lk - Lq));
         const int k = (kv_end + 127) / 128;
         return min(max(k, 0), PLAN_MAX_KEY);
     };
@@ -44,29 +45,47 @@ __global__ void __launch_bounds__(PLAN_THREADS) attn_plan_kernel(
             decode_rows[atomicAdd(&n_decode, 1)] = b;
             continue;
         }
-        const int tiles = (Lq + PLAN_TILE_ROWS - 1) / PLAN_TILE_ROWS;
+        const int tiles = (Lq + tile_rows - 1) / tile_rows;
         for (int mt = 0; mt < tiles; ++mt) atomicAdd(&hist[key_of(mt, Lq, Lk)], 1);
     }
     __syncthreads();
-    // descending exclusive scan (serial over 2048 bins by one warp's lane 0 is ~2 us; fine once per step)
-    if (threadIdx.x == 0) {
-        int run = 0;
-        for (int k = PLAN_MAX_KEY; k >= 0; --k) {
-            const int c = hist[k];
-            hist[k] = run;
-            run += c;
+    // descending exclusive scan over the bins: thread i owns bin (MAX_KEY - i)
+    {
+        const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+        const int mine = hist[PLAN_MAX_KEY - threadIdx.x];
+        int inc = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += v;
         }
-        plan[0] = run;                       // number of prefill work items
-        plan[1] = n_decode;                  // number of single-token rows
-        plan[2] = 0;
-        plan[3] = 0;
+        if (lane == 31) warp_tot[wid] = inc;
+        __syncthreads();
+        if (wid == 0) {
+            int w = warp_tot[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += v;
+            }
+            warp_tot[lane] = w;                       // inclusive totals of warps 0..lane
+        }
+        __syncthreads();
+        const int before = (wid > 0 ? warp_tot[wid - 1] : 0) + inc - mine;
+        hist[PLAN_MAX_KEY - threadIdx.x] = before;    // first position of this key (heavier keys come first)
+        if (threadIdx.x == PLAN_THREADS - 1) {
+            plan[0] = before + mine;                  // number of prefill work items
+            plan[1] = n_decode;                       // number of single-token rows
+            plan[2] = tile_rows;
+            plan[3] = 0;
+        }
     }
     __syncthreads();
     // pass 2: scatter the items to their sorted positions
     for (int b = threadIdx.x; b < batch; b += PLAN_THREADS) {
         const int Lq = cu_q[b + 1] - cu_q[b], Lk = cu_k[b + 1] - cu_k[b];
         if (Lq <= 0 || (route_decode && Lq == 1)) continue;
-        const int tiles = (Lq + PLAN_TILE_ROWS - 1) / PLAN_TILE_ROWS;
+        const int tiles = (Lq + tile_rows - 1) / tile_rows;
         for (int mt = tiles - 1; mt >= 0; --mt) {
             const int pos = atomicAdd(&hist[key_of(mt, Lq, Lk)], 1);
             if (pos < max_items) { items[2 * pos] = b; items[2 * pos + 1] = mt; }
@@ -74,9 +93,9 @@ __global__ void __launch_bounds__(PLAN_THREADS) attn_plan_kernel(
     }
 }
 
-int launch_attn_plan(const int32_t* cu_q, const int32_t* cu_k, int32_t batch, int32_t route_decode,
+int launch_attn_plan(const int32_t* cu_q, const int32_t* cu_k, int32_t batch, int32_t route_decode, int32_t tile_rows,
                      int32_t* plan, int32_t max_items, cudaStream_t stream) {
-    attn_plan_kernel<<<1, PLAN_THREADS, 0, stream>>>(cu_q, cu_k, batch, route_decode, plan, max_items);
+    attn_plan_kernel<<<1, PLAN_THREADS, 0, stream>>>(cu_q, cu_k, batch, route_decode, tile_rows, plan, max_items);
     return (int)cudaGetLastError();
 }
 

@@ -3,8 +3,8 @@
 // Same tile math as attn_prefill_tc.cu (TMA-staged Q/K/V, tcgen05.mma with S and O in TMEM, P fed
 // back to the tensor core from TMEM, two 128-row query tiles ping-ponging per CTA), restructured
 // around a device-built work list (attn_plan.cu):
-//   * one CTA per SM loops over work units (256-row query tile of one sequence x one q head) taken
-//     round-robin from a list sorted by descending KV length, so a causal batch is load-balanced
+//   * one CTA per SM loops over work units (two 128-row query tiles sharing one K/V stream: the same
+//     rows of two q heads of a GQA group, or two consecutive row tiles of one head) taken round-robin from a list sorted by descending KV length, so a causal batch is load-balanced
 //     and rows with a single query token never reach this kernel (they go to the decode kernel);
 //   * barrier phases run on counters that survive across units, so the producer prefetches the
 //     next unit's Q/K/V while the current unit drains and TMEM/smem/barriers are set up once;
@@ -25,7 +25,7 @@ namespace b200 {
 struct PersistParams {
     const int32_t* cu_q; const int32_t* cu_k; const int32_t* block_tables; int32_t bt_row_stride;
     __nv_bfloat16* out; int64_t out_token_stride;
-    int32_t Hq, G; float scale_log2;
+    int32_t Hq, G, pair_heads; float scale_log2;
     const int32_t* plan; const int32_t* items;
 };
 
@@ -42,29 +42,42 @@ struct PsSmem {
     static constexpr int ALLOC = TOTAL + 1024;
 };
 
+// One work unit = two 128-row query tiles that share one stream of K/V tiles:
+//   head-pair mode (even GQA group): the SAME rows of two q heads of one kv head (128-row items);
+//   row-pair mode  (odd group, e.g. 5): two consecutive row tiles of one q head (256-row items).
 struct Unit {
-    int b, head, q0, Lq, k0, Lk, m0, n_t0, n_t1, n_max;
+    int b, q0, Lq, k0, Lk, kvh, head0, head1, r0, r1, n_t0, n_t1, n_max;
     __device__ __forceinline__ int nt(int t) const { return t == 0 ? n_t0 : n_t1; }
+    __device__ __forceinline__ int head(int t) const { return t == 0 ? head0 : head1; }
+    __device__ __forceinline__ int rbegin(int t) const { return t == 0 ? r0 : r1; }
 };
 
-// Work unit w of this launch: (item w / Hq, head w % Hq).  Every role evaluates this itself.
+// Work unit w of this launch.  Every role evaluates this itself (a handful of cached loads).
 __device__ __forceinline__ bool get_unit(const PersistParams& p, int w, Unit& u) {
     const int n_items = __ldg(p.plan);
-    if (w >= n_items * p.Hq) return false;
-    const int item = w / p.Hq;
-    u.head = w - item * p.Hq;
+    const int per_item = p.pair_heads ? (p.Hq >> 1) : p.Hq;
+    if (w >= n_items * per_item) return false;
+    const int item = w / per_item;
+    const int sub = w - item * per_item;
     u.b = __ldg(p.items + 2 * item);
     const int mt = __ldg(p.items + 2 * item + 1);
     u.q0 = __ldg(p.cu_q + u.b);
     u.Lq = __ldg(p.cu_q + u.b + 1) - u.q0;
     u.k0 = __ldg(p.cu_k + u.b);
     u.Lk = __ldg(p.cu_k + u.b + 1) - u.k0;
-    u.m0 = mt * PLAN_TILE_ROWS;
+    if (p.pair_heads) {
+        u.head0 = 2 * sub; u.head1 = 2 * sub + 1;
+        u.r0 = u.r1 = mt * TC_BM;
+    } else {
+        u.head0 = u.head1 = sub;
+        u.r0 = mt * 2 * TC_BM; u.r1 = u.r0 + TC_BM;
+    }
+    u.kvh = u.head0 / p.G;
     const int offset = u.Lk - u.Lq;
-    int kv_end0 = min(u.Lk, u.m0 + TC_BM + offset);
-    if (u.m0 >= u.Lq || kv_end0 < 0) kv_end0 = 0;
-    int kv_end1 = min(u.Lk, u.m0 + 2 * TC_BM + offset);
-    if (u.m0 + TC_BM >= u.Lq || kv_end1 < 0) kv_end1 = 0;
+    int kv_end0 = min(u.Lk, u.r0 + TC_BM + offset);
+    if (u.r0 >= u.Lq || kv_end0 < 0) kv_end0 = 0;
+    int kv_end1 = min(u.Lk, u.r1 + TC_BM + offset);
+    if (u.r1 >= u.Lq || kv_end1 < 0) kv_end1 = 0;
     u.n_t0 = (kv_end0 + TC_BN - 1) / TC_BN;
     u.n_t1 = (kv_end1 + TC_BN - 1) / TC_BN;
     u.n_max = max(u.n_t0, u.n_t1);
@@ -163,20 +176,20 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
                 uint32_t kv_it = 0, q_use0 = 0, q_use1 = 0;
                 Unit u;
                 for (int w = blockIdx.x; get_unit(p, w, u); w += gridDim.x) {
-                    const int kvh = u.head / p.G;
+                    const int kvh = u.kvh;
                     if (u.n_t0 > 0) {
                         mbar_wait(q_empty(0), (q_use0 & 1u) ^ 1u);
                         ++q_use0;
                         mbar_expect_tx(q_full(0), TC_TILE_BYTES);
-                        tma_load_3d(sQ, &map_q, q_full(0), 0, u.head, u.q0 + u.m0);
-                        tma_load_3d(sQ + TC_HALF_BYTES, &map_q, q_full(0), 64, u.head, u.q0 + u.m0);
+                        tma_load_3d(sQ, &map_q, q_full(0), 0, u.head0, u.q0 + u.r0);
+                        tma_load_3d(sQ + TC_HALF_BYTES, &map_q, q_full(0), 64, u.head0, u.q0 + u.r0);
                     }
                     if (u.n_t1 > 0) {
                         mbar_wait(q_empty(1), (q_use1 & 1u) ^ 1u);
                         ++q_use1;
                         mbar_expect_tx(q_full(1), TC_TILE_BYTES);
-                        tma_load_3d(sQ + TC_TILE_BYTES, &map_q, q_full(1), 0, u.head, u.q0 + u.m0 + TC_BM);
-                        tma_load_3d(sQ + TC_TILE_BYTES + TC_HALF_BYTES, &map_q, q_full(1), 64, u.head, u.q0 + u.m0 + TC_BM);
+                        tma_load_3d(sQ + TC_TILE_BYTES, &map_q, q_full(1), 0, u.head1, u.q0 + u.r1);
+                        tma_load_3d(sQ + TC_TILE_BYTES + TC_HALF_BYTES, &map_q, q_full(1), 64, u.head1, u.q0 + u.r1);
                     }
                     const int32_t* bt = paged ? p.block_tables + (int64_t)u.b * p.bt_row_stride : nullptr;
                     for (int j = 0; j < u.n_max; ++j, ++kv_it) {
@@ -276,7 +289,7 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
         Unit u;
         for (int w = blockIdx.x; get_unit(p, w, u); w += gridDim.x) {
             const int nt = u.nt(t);
-            const int r_begin = u.m0 + t * TC_BM;
+            const int r_begin = u.rbegin(t);
             const int row = r_begin + row_in_tile;                  // query index within the sequence
             const int offset = u.Lk - u.Lq;
             float m_used = -INFINITY;                               // running maximum, scaled (log2) domain
@@ -371,7 +384,7 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
                 unpack2(l2, la, lb);
                 const float l_sum = la + lb;
                 const float inv = l_sum > 0.f ? 1.f / l_sum : 0.f;
-                __nv_bfloat16* orow = p.out + (int64_t)(u.q0 + row) * p.out_token_stride + (int64_t)u.head * B200_HD;
+                __nv_bfloat16* orow = p.out + (int64_t)(u.q0 + row) * p.out_token_stride + (int64_t)u.head(t) * B200_HD;
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
                     uint32_t o[32];
@@ -429,8 +442,9 @@ int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32
     p.cu_q = a.cu_q; p.cu_k = a.cu_k; p.block_tables = a.block_tables; p.bt_row_stride = a.bt_row_stride;
     p.out = (__nv_bfloat16*)a.out; p.out_token_stride = a.out_token_stride;
     p.Hq = a.Hq; p.G = a.Hq / a.Hkv; p.scale_log2 = a.scale * 1.4426950408889634f;
+    p.pair_heads = plan_tile_rows(a.Hq, a.Hkv) == 128 ? 1 : 0;
     p.plan = plan; p.items = plan + PLAN_HEADER_WORDS + a.batch;
-    int64_t units = (int64_t)max_items * a.Hq;
+    int64_t units = (int64_t)max_items * (p.pair_heads ? a.Hq / 2 : a.Hq);
     int grid = sm_count();
     if (units < grid) grid = (int)units;
     if (grid < 1) grid = 1;

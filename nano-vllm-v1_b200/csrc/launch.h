@@ -50,16 +50,18 @@ int launch_attn_prefill_tc1(const PrefillArgs& a, cudaStream_t stream);  // same
 bool prefill_tc_available();
 
 // ---- step plan (attn_plan.cu) + persistent tcgen05 prefill (attn_prefill_persist.cu) ----------
-// plan buffer, int32 words: [0] n_items  [1] n_decode_rows  [2..15] reserved
+// plan buffer, int32 words: [0] n_items  [1] n_decode_rows  [2] tile_rows  [3..15] reserved
 //                           [16 .. 16 + batch)        rows with exactly one query token
-//                           [.. + 2*max_items)        (sequence, 256-row tile) pairs, heaviest first
+//                           [.. + 2*max_items)        (sequence, query tile) pairs, heaviest first; plan[2] = tile rows
 constexpr int PLAN_HEADER_WORDS = 16;
-constexpr int PLAN_TILE_ROWS = 256;
-inline int32_t plan_max_items(int32_t batch, int32_t total_q) { return total_q / PLAN_TILE_ROWS + batch; }
+constexpr int PLAN_TILE_ROWS_MIN = 128;
+// tile rows of a launch: 128 when two q heads of one kv head share a CTA (even GQA group), else 256
+inline int32_t plan_tile_rows(int32_t Hq, int32_t Hkv) { return ((Hq / Hkv) % 2 == 0) ? 128 : 256; }
+inline int32_t plan_max_items(int32_t batch, int32_t total_q) { return total_q / PLAN_TILE_ROWS_MIN + batch; }
 inline size_t plan_bytes(int32_t batch, int32_t total_q) {
     return ((size_t)PLAN_HEADER_WORDS + 2 * (size_t)plan_max_items(batch, total_q) + (size_t)batch) * sizeof(int32_t);
 }
-int launch_attn_plan(const int32_t* cu_q, const int32_t* cu_k, int32_t batch, int32_t route_decode,
+int launch_attn_plan(const int32_t* cu_q, const int32_t* cu_k, int32_t batch, int32_t route_decode, int32_t tile_rows,
                      int32_t* plan, int32_t max_items, cudaStream_t stream);
 int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32_t max_items, cudaStream_t stream);
 

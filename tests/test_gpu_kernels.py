@@ -223,10 +223,11 @@ def test_planned_paged_mixed_vs_oracle(ops, Hq, Hkv):
     want = oracle.attn_varlen(c["q"], c["k_cache"], c["v_cache"], c["cu_seqlens_q"], c["cu_seqlens_k"], SCALE,
                               c["block_tables"])
     cu_q, cu_k = dev(c["cu_seqlens_q"]), dev(c["cu_seqlens_k"])
-    plan = ops.attn_plan(cu_q, cu_k, sum(lens_q), route_decode=True)
+    plan = ops.attn_plan(cu_q, cu_k, sum(lens_q), Hq, Hkv, route_decode=True)
     n_items, n_dec = plan.counts()
+    tile = 128 if (Hq // Hkv) % 2 == 0 else 256            # head-pair vs row-pair units
     assert n_dec == sum(1 for x in lens_q if x == 1)
-    assert n_items == sum((x + 255) // 256 for x in lens_q if x > 1)
+    assert n_items == sum((x + tile - 1) // tile for x in lens_q if x > 1)
     got = torch.full_like(dev(c["q"]), float("nan"))
     for _ in range(2):                                       # the same plan serves every layer of a step
         ops.attn_varlen_planned(dev(c["q"]), dev(c["k_cache"]), dev(c["v_cache"]), cu_q, cu_k, c["max_seqlen_q"],

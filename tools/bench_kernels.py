@@ -117,6 +117,16 @@ def prefill_case(name, lens_q, lens_k, Hq, Hkv, iters, results, variants=(2, 1),
                     f"{tag}_frac_bf16_burst": flops / med / 1e9 / PEAK["bf16_tflops"],
                     f"{tag}_frac_bf16_sustained": flops / med / 1e9 / PEAK["bf16_tflops_sustained"]})
         outs[tag] = fn()
+    # planned path: persistent tcgen05 kernel (+ decode kernel for single-token rows); the plan is built
+    # once per engine step and shared by all layers, so it is timed separately
+    plan = ops.attn_plan(cu_q, cu_k, T, Hq, Hkv, route_decode=True)
+    pmed, _ = timeit(lambda: ops.attn_plan(cu_q, cu_k, T, Hq, Hkv, route_decode=True), iters, warm=2)
+    fn = lambda: ops.attn_varlen_planned(q, kc, vc, cu_q, cu_k, max(lens_q), max(lens_k), SCALE, block_table=bt, plan=plan)  # noqa: E731
+    med, best = timeit(fn, iters, warm=2)
+    rec.update({"ps_ms_median": med, "ps_ms_best": best, "ps_tflops": flops / med / 1e9, "plan_ms_median": pmed,
+                "ps_frac_bf16_burst": flops / med / 1e9 / PEAK["bf16_tflops"],
+                "ps_frac_bf16_sustained": flops / med / 1e9 / PEAK["bf16_tflops_sustained"]})
+    outs["ps"] = fn()
     if flash_attn is not None:
         fa = lambda: flash_attn.flash_attn_varlen_func(q, kc, vc, cu_seqlens_q=cu_q, cu_seqlens_k=cu_k, max_seqlen_q=max(lens_q),  # noqa: E731
                                                        max_seqlen_k=max(lens_k), softmax_scale=SCALE, causal=True, block_table=bt)
