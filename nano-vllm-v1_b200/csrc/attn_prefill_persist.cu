@@ -52,6 +52,10 @@ struct Unit {
     __device__ __forceinline__ int rbegin(int t) const { return t == 0 ? r0 : r1; }
 };
 
+// Round k of CTA c takes unit snake(k, c): the list is sorted heaviest-first, so alternating the
+// direction of every other round pairs a CTA's heavy units with light ones (static LPT-like balance).
+__device__ __forceinline__ int snake(int k, int c, int g) { return (k & 1) ? (k + 1) * g - 1 - c : k * g + c; }
+
 // Work unit w of this launch.  Every role evaluates this itself (a handful of cached loads).
 __device__ __forceinline__ bool get_unit(const PersistParams& p, int w, Unit& u) {
     const int n_items = __ldg(p.plan);
@@ -82,6 +86,12 @@ __device__ __forceinline__ bool get_unit(const PersistParams& p, int w, Unit& u)
     u.n_t1 = (kv_end1 + TC_BN - 1) / TC_BN;
     u.n_max = max(u.n_t0, u.n_t1);
     return true;
+}
+
+// A CTA stops at its first out-of-range round: if snake(k, c) >= n then n < (k+1)*g, so every index of
+// every later round is out of range as well.
+__device__ __forceinline__ bool get_round(const PersistParams& p, int k, Unit& u) {
+    return get_unit(p, snake(k, (int)blockIdx.x, (int)gridDim.x), u);
 }
 
 // ---- packed f32x2 arithmetic (sm_100: FFMA2 / FADD2) and 3-input max ---------------------------
@@ -175,7 +185,7 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
                 const bool paged = p.block_tables != nullptr;
                 uint32_t kv_it = 0, q_use0 = 0, q_use1 = 0;
                 Unit u;
-                for (int w = blockIdx.x; get_unit(p, w, u); w += gridDim.x) {
+                for (int k = 0; get_round(p, k, u); ++k) {
                     const int kvh = u.kvh;
                     if (u.n_t0 > 0) {
                         mbar_wait(q_empty(0), (q_use0 & 1u) ^ 1u);
@@ -230,7 +240,7 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
                 };
                 uint32_t kv_it = 0, q_use[2] = {0, 0}, p_cnt[2] = {0, 0};
                 Unit u;
-                for (int w = blockIdx.x; get_unit(p, w, u); w += gridDim.x) {
+                for (int k = 0; get_round(p, k, u); ++k) {
 #pragma unroll
                     for (int t = 0; t < 2; ++t)
                         if (u.nt(t) > 0) { mbar_wait(q_full(t), q_use[t] & 1u); ++q_use[t]; }
@@ -287,7 +297,7 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
         const uint64_t scale2 = pack2(p.scale_log2, p.scale_log2);
         uint32_t s_cnt = 0, o_cnt = 0, kv_it = 0;
         Unit u;
-        for (int w = blockIdx.x; get_unit(p, w, u); w += gridDim.x) {
+        for (int k = 0; get_round(p, k, u); ++k) {
             const int nt = u.nt(t);
             const int r_begin = u.rbegin(t);
             const int row = r_begin + row_in_tile;                  // query index within the sequence
