@@ -31,11 +31,12 @@ __global__ void __launch_bounds__(256) kv_scatter_kernel(
 }
 
 // ------------------------------------------------------------------------------------------
-// (4a) q_norm/k_norm + RoPE.  One warp per (token, head) row of 128 bf16.
-//      Lane l owns elements {2l, 2l+1} of the low half and {64+2l, 65+2l} of the high half,
-//      i.e. both members of two NeoX rotation pairs => no cross-lane traffic for the rotation,
-//      one butterfly for the sum of squares.  Roundings follow layernorm.py:85-93 and
-//      rotary_embedding.py:60-65 exactly: bf16(x*rstd), bf16(.*w), fp32 rotate, bf16.
+// (4a) q_norm/k_norm + RoPE.  Eight lanes per (token, head) row of 128 bf16, four rows per warp.
+//      Lane l owns elements [8l, 8l+8) of the low half and [64+8l, 64+8l+8) of the high half,
+//      i.e. both members of eight NeoX rotation pairs => two 16-byte loads + two 16-byte stores
+//      per lane, no cross-lane traffic for the rotation, a 3-step butterfly for the sum of squares.
+//      Roundings follow layernorm.py:85-93 and rotary_embedding.py:60-65 exactly:
+//      bf16(x*rstd), bf16(.*w), fp32 rotate (un-fused mul/sub), bf16.
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) qk_norm_rope_kernel(
     const __nv_bfloat16* __restrict__ q, int64_t q_token_stride,
@@ -44,45 +45,73 @@ __global__ void __launch_bounds__(256) qk_norm_rope_kernel(
     const __nv_bfloat16* __restrict__ q_weight, const __nv_bfloat16* __restrict__ k_weight, float eps,
     __nv_bfloat16* __restrict__ q_out, __nv_bfloat16* __restrict__ k_out,
     int64_t total_rows, int32_t Hq, int32_t Hkv) {
-    const int lane = threadIdx.x & 31;
-    const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (row >= total_rows) return;
+    const int sub = threadIdx.x & 7;
+    const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+    const bool live = row < total_rows;                        // dead lanes still take part in the shuffles
     const int32_t H = Hq + Hkv;
-    const int64_t tok = row / H;
-    const int32_t h = (int32_t)(row - tok * H);
+    const int64_t tok = live ? row / H : 0;
+    const int32_t h = live ? (int32_t)(row - tok * H) : 0;
     const bool is_q = h < Hq;
     const __nv_bfloat16* src = is_q ? q + tok * q_token_stride + (int64_t)h * B200_HD
                                     : k + tok * k_token_stride + (int64_t)(h - Hq) * B200_HD;
     __nv_bfloat16* dst = is_q ? q_out + (tok * Hq + h) * B200_HD : k_out + (tok * Hkv + (h - Hq)) * B200_HD;
     const __nv_bfloat16* w = is_q ? q_weight : k_weight;
 
-    const float2 lo = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(src + 2 * lane));
-    const float2 hi = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(src + 64 + 2 * lane));
-    float ss = lo.x * lo.x + lo.y * lo.y + hi.x * hi.x + hi.y * hi.y;
+    int4 lo4 = make_int4(0, 0, 0, 0), hi4 = lo4;
+    if (live) {
+        lo4 = ld_nc_v4(src + 8 * sub);
+        hi4 = ld_nc_v4(src + 64 + 8 * sub);
+    }
+    const uint32_t lo_u[4] = {(uint32_t)lo4.x, (uint32_t)lo4.y, (uint32_t)lo4.z, (uint32_t)lo4.w};
+    const uint32_t hi_u[4] = {(uint32_t)hi4.x, (uint32_t)hi4.y, (uint32_t)hi4.z, (uint32_t)hi4.w};
+    float x1[8], x2[8];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-    const float rstd = rsqrtf(__fadd_rn(ss * (1.0f / B200_HD), eps));
-    // weight == nullptr => rotation only (stand-alone RotaryEmbedding.forward)
-    const float2 wlo = w ? unpack_bf16x2(*reinterpret_cast<const uint32_t*>(w + 2 * lane)) : make_float2(1.f, 1.f);
-    const float2 whi = w ? unpack_bf16x2(*reinterpret_cast<const uint32_t*>(w + 64 + 2 * lane)) : make_float2(1.f, 1.f);
-    // bf16(x * rstd) then bf16(that * w): two roundings, as in the reference
-    auto nrm = [&](float x, float wt) {
-        if (w == nullptr) return x;
-        const float y = __bfloat162float(__float2bfloat16_rn(__fmul_rn(x, rstd)));
-        return __bfloat162float(__float2bfloat16_rn(__fmul_rn(y, wt)));
-    };
-    const float x1a = nrm(lo.x, wlo.x), x1b = nrm(lo.y, wlo.y);
-    const float x2a = nrm(hi.x, whi.x), x2b = nrm(hi.y, whi.y);
-    const float* cs = cos_sin + positions[tok] * B200_HD;                 // [cos(64) | sin(64)]
-    const float2 c = *reinterpret_cast<const float2*>(cs + 2 * lane);
-    const float2 s = *reinterpret_cast<const float2*>(cs + 64 + 2 * lane);
-    // y1 = x1*cos - x2*sin ; y2 = x2*cos + x1*sin  (un-fused, matching eager fp32)
-    const float y1a = __fsub_rn(__fmul_rn(x1a, c.x), __fmul_rn(x2a, s.x));
-    const float y1b = __fsub_rn(__fmul_rn(x1b, c.y), __fmul_rn(x2b, s.y));
-    const float y2a = __fadd_rn(__fmul_rn(x2a, c.x), __fmul_rn(x1a, s.x));
-    const float y2b = __fadd_rn(__fmul_rn(x2b, c.y), __fmul_rn(x1b, s.y));
-    *reinterpret_cast<uint32_t*>(dst + 2 * lane) = pack_bf16x2(y1a, y1b);
-    *reinterpret_cast<uint32_t*>(dst + 64 + 2 * lane) = pack_bf16x2(y2a, y2b);
+    for (int j = 0; j < 4; ++j) {
+        const float2 a = unpack_bf16x2(lo_u[j]), b = unpack_bf16x2(hi_u[j]);
+        x1[2 * j] = a.x; x1[2 * j + 1] = a.y;
+        x2[2 * j] = b.x; x2[2 * j + 1] = b.y;
+    }
+    if (w != nullptr) {                                        // nullptr => rotation only (RotaryEmbedding.forward)
+        float ss = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) ss += x1[j] * x1[j] + x2[j] * x2[j];
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+        const float rstd = rsqrtf(__fadd_rn(ss * (1.0f / B200_HD), eps));
+        const int4 wl4 = *reinterpret_cast<const int4*>(w + 8 * sub);
+        const int4 wh4 = *reinterpret_cast<const int4*>(w + 64 + 8 * sub);
+        const uint32_t wl_u[4] = {(uint32_t)wl4.x, (uint32_t)wl4.y, (uint32_t)wl4.z, (uint32_t)wl4.w};
+        const uint32_t wh_u[4] = {(uint32_t)wh4.x, (uint32_t)wh4.y, (uint32_t)wh4.z, (uint32_t)wh4.w};
+        // bf16(x * rstd) then bf16(that * w): two roundings, as in the reference
+        auto nrm = [&](float x, float wt) {
+            const float y = __bfloat162float(__float2bfloat16_rn(__fmul_rn(x, rstd)));
+            return __bfloat162float(__float2bfloat16_rn(__fmul_rn(y, wt)));
+        };
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float2 a = unpack_bf16x2(wl_u[j]), b = unpack_bf16x2(wh_u[j]);
+            x1[2 * j] = nrm(x1[2 * j], a.x); x1[2 * j + 1] = nrm(x1[2 * j + 1], a.y);
+            x2[2 * j] = nrm(x2[2 * j], b.x); x2[2 * j + 1] = nrm(x2[2 * j + 1], b.y);
+        }
+    }
+    if (!live) return;
+    const float* cs = cos_sin + positions[tok] * B200_HD + 8 * sub;       // [cos(64) | sin(64)]
+    const float4 c0 = *reinterpret_cast<const float4*>(cs), c1 = *reinterpret_cast<const float4*>(cs + 4);
+    const float4 s0 = *reinterpret_cast<const float4*>(cs + 64), s1 = *reinterpret_cast<const float4*>(cs + 68);
+    const float c[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+    const float s[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+    uint32_t y1[4], y2[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        // y1 = x1*cos - x2*sin ; y2 = x2*cos + x1*sin  (un-fused, matching eager fp32)
+        const int a = 2 * j, b = 2 * j + 1;
+        y1[j] = pack_bf16x2(__fsub_rn(__fmul_rn(x1[a], c[a]), __fmul_rn(x2[a], s[a])),
+                            __fsub_rn(__fmul_rn(x1[b], c[b]), __fmul_rn(x2[b], s[b])));
+        y2[j] = pack_bf16x2(__fadd_rn(__fmul_rn(x2[a], c[a]), __fmul_rn(x1[a], s[a])),
+                            __fadd_rn(__fmul_rn(x2[b], c[b]), __fmul_rn(x1[b], s[b])));
+    }
+    st_v4(dst + 8 * sub, make_int4(y1[0], y1[1], y1[2], y1[3]));
+    st_v4(dst + 64 + 8 * sub, make_int4(y2[0], y2[1], y2[2], y2[3]));
 }
 
 // ------------------------------------------------------------------------------------------
@@ -244,7 +273,7 @@ int launch_qk_norm_rope(const void* q, int64_t q_token_stride, const void* k, in
                         const int64_t* positions, const float* cos_sin, const void* qw, const void* kw, float eps,
                         void* q_out, void* k_out, int32_t T, int32_t Hq, int32_t Hkv, cudaStream_t stream) {
     const int64_t rows = (int64_t)T * (Hq + Hkv);
-    const int64_t blocks = (rows + 7) / 8;
+    const int64_t blocks = (rows + 31) / 32;                      // 8 lanes per row, 256 threads
     qk_norm_rope_kernel<<<(unsigned)blocks, 256, 0, stream>>>(
         (const __nv_bfloat16*)q, q_token_stride, (const __nv_bfloat16*)k, k_token_stride, positions, cos_sin,
         (const __nv_bfloat16*)qw, (const __nv_bfloat16*)kw, eps, (__nv_bfloat16*)q_out, (__nv_bfloat16*)k_out,
