@@ -145,6 +145,10 @@ def run_ours(args):
     assert HKV % world == 0
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
+    # NCCL may print its version banner on stdout; keep stdout for the one JSON line
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
         dist.init_process_group("nccl", device_id=device)
     b200attn.load_library()
@@ -255,6 +259,8 @@ def run_ours(args):
             "cpu_baseline": cpu,
             "clocks": clocks,
         }
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -158,6 +158,25 @@ int b200_qk_norm_rope(const void* q, int64_t q_token_stride,
                       int32_t num_tokens, int32_t num_heads, int32_t num_kv_heads,
                       int32_t head_dim, void* stream);
 
+/* (4a + 1) The same q/k RMSNorm + RoPE, and in the SAME launch the KV-cache scatter of (1)
+ *      (SURVEY.md 8 f2): the rotated k row goes to k_out (may be NULL when nothing reads fresh k:
+ *      paged and decode calls read the cache) AND to k_cache[slot_mapping[t]]; the untouched v row
+ *      is copied to v_cache[slot_mapping[t]]; slot -1 skips both cache writes
+ *      (layers/attention.py:79-80).  Replaces, in one pass over qkv, models/qwen3.py:191-195 plus
+ *      store_kvcache (layers/attention.py:93-127, called at :219-220).  Caches are
+ *      [num_slots, Hkv, D] contiguous.  The launch completes (stream order) before any attention
+ *      kernel reads the cache, so same-step prefix sharing is unaffected.
+ */
+int b200_qk_norm_rope_store(const void* q, int64_t q_token_stride,
+                            const void* k, int64_t k_token_stride,
+                            const void* v, int64_t v_token_stride,
+                            const int64_t* positions, const float* cos_sin_cache,
+                            const void* q_weight, const void* k_weight, float eps,
+                            void* q_out, void* k_out,
+                            void* k_cache, void* v_cache, const int32_t* slot_mapping,
+                            int32_t num_tokens, int32_t num_heads, int32_t num_kv_heads,
+                            int32_t head_dim, void* stream);
+
 /* (4a') RMSNorm over the hidden size with optional fused residual add.  Replaces
  *      RMSNorm.rms_forward / add_rms_forward (layernorm.py:57-141).  residual may be NULL;
  *      when given it is updated IN PLACE to round(x + residual), as the reference returns. */

@@ -32,6 +32,9 @@ SIGNATURES = {
                                           c_int32, c_void_p, c_size_t, c_void_p, c_size_t, c_void_p]),
     "b200_qk_norm_rope": (c_int32, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
                                     c_float, c_void_p, c_void_p, c_int32, c_int32, c_int32, c_int32, c_void_p]),
+    "b200_qk_norm_rope_store": (c_int32, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p,
+                                          c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                          c_int32, c_int32, c_int32, c_int32, c_void_p]),
     "b200_rmsnorm": (c_int32, [c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_int32, c_int32, c_void_p]),
     "b200_silu_and_mul": (c_int32, [c_void_p, c_void_p, c_int32, c_int32, c_void_p]),
 }

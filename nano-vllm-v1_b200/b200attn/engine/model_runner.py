@@ -10,6 +10,12 @@
                       and dtypes; built with numpy instead of per-token Python list appends,
                       staged in ONE pinned buffer and moved with ONE H2D copy (the reference
                       makes 7-8 pinned allocations + copies per step).
+  run                 model_runner.py:602-638  same pipeline and return shape; the indices of the
+                      sequences that produced a token are returned as a host list (they were built on
+                      the host in prepare_model_input) instead of the CUDA int32 tensor, so that the
+                      untouched `Scheduler.postprocess` (scheduler.py:248) no longer pays one
+                      device->host sync per sequence when it iterates them (3.6 ms of an
+                      11.7 ms Qwen3-8B decode step at 256 sequences, profiles/r1f_step_phases.json).
   capture_cudagraph   model_runner.py:640-715  unchanged logic (the reference method runs);
                       the decode kernel it captures reads every length from device memory and
                       its launch geometry depends on host integers only.
@@ -138,6 +144,21 @@ def prepare_model_input(self, seqs, _set_context):
             continue
         dt = torch.int64 if a.dtype == np.int64 else torch.int32
         out[name] = dev[offs[name]:offs[name] + a.nbytes].view(dt).view(a.shape)
+    self._b200_need_logits_host = arrays["seq_need_compute_logits"].tolist()
     _set_context(out["cu_seqlens_q"], out["cu_seqlens_k"], max_q, max_k, out["slot_mapping"], out["context_lens"],
                  out["block_tables"], out["seq_need_compute_logits"])
     return out["input_ids"], out["positions"]
+
+
+def run(self, seqs, _get_context, _reset_context):
+    """ModelRunner.run (model_runner.py:602-638): prepare -> forward -> sample; see module docstring."""
+    self._b200_need_logits_host = None
+    input_ids, positions = self.prepare_model_input(seqs)
+    temperatures = self.prepare_sample(seqs) if self.rank == 0 else None
+    logits = self.run_model(input_ids, positions)
+    token_ids = self.sampler(logits, temperatures).tolist() if self.rank == 0 else None
+    need = self._b200_need_logits_host
+    if need is None:                                       # prepare_model_input was not ours
+        need = _get_context().seq_need_compute_logits
+    _reset_context()
+    return token_ids, need

@@ -6,18 +6,20 @@ stay valid whatever was imported first:
 
     nanovllm.layers.attention.Attention.forward        -> scatter + decode / prefill kernels
     nanovllm.layers.attention.store_kvcache            -> b200_kv_scatter
-    nanovllm.models.qwen3.Qwen3Attention.forward       -> qkv_proj, ONE fused q/k-norm+RoPE launch,
-                                                          attention, o_proj (qwen3.py:183-199 order kept)
+    nanovllm.models.qwen3.Qwen3Attention.forward       -> qkv_proj, ONE fused q/k-norm+RoPE+KV-scatter launch,
+                                                          attention, o_proj (qwen3.py:183-199 order kept;
+                                                          B200ATTN_FUSE_STORE=0 keeps the scatter separate)
     nanovllm.layers.layernorm.RMSNorm.forward          -> b200_rmsnorm (fused residual add)
     nanovllm.layers.rotary_embedding.RotaryEmbedding.forward -> rotation-only kernel
     nanovllm.layers.activation.SiluAndMul.forward      -> b200_silu_and_mul
-    nanovllm.engine.model_runner.ModelRunner.{allocate_kv_cache, prepare_model_input}
+    nanovllm.engine.model_runner.ModelRunner.{allocate_kv_cache, prepare_model_input, run}
 
 `LLM.generate`, `Scheduler`, `BlockManager`, `Sequence`, the linears, the sampler and NCCL are untouched.
 `install(pointwise=False)` limits the patch to attention + scatter; `install(runner=False)`
 leaves ModelRunner alone.
 """
 import importlib
+import os
 
 import torch
 
@@ -25,6 +27,7 @@ from . import ops
 from .layers import attention as _attention
 
 _INSTALLED = False
+_FUSE_STORE = os.environ.get("B200ATTN_FUSE_STORE", "1") != "0"
 
 
 def _attention_forward(self, q, k, v):
@@ -38,12 +41,18 @@ def _qwen3_attention_forward(self, positions, hidden_states):
     k = k.view(-1, self.num_kv_heads, self.head_dim)
     v = v.view(-1, self.num_kv_heads, self.head_dim)
     rope = self.rotary_emb
-    if not self.qkv_bias:
-        q, k = ops.qk_norm_rope(q, k, positions, self.q_norm.weight, self.k_norm.weight,
-                                rope.cos_sin_cache, self.q_norm.eps)
+    wq, wk, eps = (self.q_norm.weight, self.k_norm.weight, self.q_norm.eps) if not self.qkv_bias else (None, None, 1e-6)
+    attn = self.attn
+    if _FUSE_STORE and attn.k_cache.numel() and attn.v_cache.numel():
+        # one launch: q/k norm + RoPE + KV-cache scatter; fresh k is only read by unpaged prefill
+        ctx = _attention._context()
+        need_k = ctx.cu_seqlens_q is not None and ctx.block_tables is None
+        q, k = ops.qk_norm_rope_store(q, k, v, positions, wq, wk, rope.cos_sin_cache, eps,
+                                      attn.k_cache, attn.v_cache, ctx.slot_mapping, need_k_out=need_k)
+        o = _attention.Attention.forward(attn, q, k, v, kv_stored=True)
     else:
-        q, k = ops.qk_norm_rope(q, k, positions, None, None, rope.cos_sin_cache)
-    o = self.attn(q, k, v)
+        q, k = ops.qk_norm_rope(q, k, positions, wq, wk, rope.cos_sin_cache, eps)
+        o = attn(q, k, v)
     return self.o_proj(o.flatten(1, -1))
 
 
@@ -84,6 +93,7 @@ def install(pointwise: bool = True, runner: bool = True) -> None:
         ref_alloc = mr.ModelRunner.allocate_kv_cache
         mr.ModelRunner.allocate_kv_cache = lambda self: ours.allocate_kv_cache(self, ref_alloc)
         mr.ModelRunner.prepare_model_input = lambda self, seqs: ours.prepare_model_input(self, seqs, ctx.set_context)
+        mr.ModelRunner.run = lambda self, seqs: ours.run(self, seqs, ctx.get_context, ctx.reset_context)
     _INSTALLED = True
 
 

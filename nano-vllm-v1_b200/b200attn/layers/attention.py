@@ -53,10 +53,13 @@ class Attention(nn.Module):
         self.num_kv_heads = num_kv_heads
         self.k_cache = self.v_cache = torch.tensor([])
 
-    def forward(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor):
+    def forward(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, kv_stored: bool = False):
+        """`kv_stored=True`: the caller already wrote this step's K/V into the caches (the fused
+        norm+rope+store launch, ops.qk_norm_rope_store) -- skip the scatter; `k` may then be None
+        when the call reads K/V from the cache (paged or decode)."""
         context = _context()
         k_cache, v_cache = self.k_cache, self.v_cache
-        if k_cache.numel() and v_cache.numel():
+        if not kv_stored and k_cache.numel() and v_cache.numel():
             store_kvcache(k, v, k_cache, v_cache, context.slot_mapping)
         if context.cu_seqlens_q is None:
             # CUDA-graph decode form: one query token per row, lengths in context_lens

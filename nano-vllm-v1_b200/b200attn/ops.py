@@ -260,6 +260,34 @@ def qk_norm_rope(q: torch.Tensor, k: torch.Tensor, positions: torch.Tensor, q_we
     return q_out, k_out
 
 
+def qk_norm_rope_store(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, positions: torch.Tensor,
+                       q_weight: Optional[torch.Tensor], k_weight: Optional[torch.Tensor], cos_sin_cache: torch.Tensor,
+                       eps: float, k_cache: torch.Tensor, v_cache: torch.Tensor, slot_mapping: torch.Tensor,
+                       need_k_out: bool = True) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    """qk_norm_rope + store_kvcache in one launch.  Returns (q', k' or None); k' (rotated)
+    and v are in the caches at `slot_mapping` when this returns (stream order)."""
+    T, Hq, D = q.shape
+    Hkv = k.shape[1]
+    for t, n in ((q, "q"), (k, "k"), (v, "v"), (k_cache, "k_cache"), (v_cache, "v_cache")):
+        _need_cuda_bf16(t, n)
+    _need_i32(slot_mapping, "slot_mapping")
+    assert q.stride(-1) == 1 and q.stride(1) == D and k.stride(-1) == 1 and k.stride(1) == D
+    assert v.stride(-1) == 1 and v.stride(1) == D and v.shape == k.shape
+    assert k_cache.stride(1) == Hkv * D and v_cache.stride(1) == Hkv * D and k_cache.is_contiguous() and v_cache.is_contiguous()
+    assert slot_mapping.numel() == T
+    assert positions.dtype == torch.int64 and positions.is_cuda and positions.is_contiguous()
+    assert cos_sin_cache.dtype == torch.float32 and cos_sin_cache.is_contiguous() and cos_sin_cache.shape[-1] == D
+    q_out = torch.empty((T, Hq, D), dtype=q.dtype, device=q.device)
+    k_out = torch.empty((T, Hkv, D), dtype=k.dtype, device=k.device) if need_k_out else None
+    check(load_library().b200_qk_norm_rope_store(
+        q.data_ptr(), q.stride(0), k.data_ptr(), k.stride(0), v.data_ptr(), v.stride(0),
+        positions.data_ptr(), cos_sin_cache.data_ptr(),
+        q_weight.data_ptr() if q_weight is not None else None, k_weight.data_ptr() if k_weight is not None else None,
+        float(eps), q_out.data_ptr(), k_out.data_ptr() if k_out is not None else None,
+        k_cache.data_ptr(), v_cache.data_ptr(), slot_mapping.data_ptr(), T, Hq, Hkv, D, _stream()), "b200_qk_norm_rope_store")
+    return q_out, k_out
+
+
 def rms_norm(x: torch.Tensor, weight: torch.Tensor, eps: float, residual: Optional[torch.Tensor] = None):
     """layernorm.py:143-165.  With `residual`, returns (normed, residual_out) like the reference;
     residual is updated in place."""

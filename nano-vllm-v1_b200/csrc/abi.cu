@@ -246,11 +246,31 @@ int b200_qk_norm_rope(const void* q, int64_t q_token_stride, const void* k, int6
     if (num_tokens == 0) return B200_OK;
     if (!q || !k || !positions || !cos_sin_cache || !q_out || !k_out) return B200_ERR_NULL;   /* NULL weights => rotation only */
     if (head_dim != B200_HD_CONST) return B200_ERR_SHAPE;
-    if ((reinterpret_cast<uintptr_t>(q) & 3) || (reinterpret_cast<uintptr_t>(k) & 3) || (q_token_stride & 1) ||
-        (k_token_stride & 1) || (reinterpret_cast<uintptr_t>(cos_sin_cache) & 7))
-        return B200_ERR_ALIGN;
+    if (!aligned16(q) || !aligned16(k) || !aligned16(q_out) || !aligned16(k_out) || !stride_ok(q_token_stride) ||
+        !stride_ok(k_token_stride) || (reinterpret_cast<uintptr_t>(cos_sin_cache) & 15))
+        return B200_ERR_ALIGN;                                      /* the kernel uses 16-byte accesses throughout */
     return launch_qk_norm_rope(q, q_token_stride, k, k_token_stride, positions, cos_sin_cache, q_weight, k_weight,
                                eps, q_out, k_out, num_tokens, num_heads, num_kv_heads, (cudaStream_t)stream);
+}
+
+int b200_qk_norm_rope_store(const void* q, int64_t q_token_stride, const void* k, int64_t k_token_stride,
+                            const void* v, int64_t v_token_stride,
+                            const int64_t* positions, const float* cos_sin_cache, const void* q_weight,
+                            const void* k_weight, float eps, void* q_out, void* k_out,
+                            void* k_cache, void* v_cache, const int32_t* slot_mapping,
+                            int32_t num_tokens, int32_t num_heads, int32_t num_kv_heads, int32_t head_dim, void* stream) {
+    if (num_tokens < 0 || num_heads <= 0 || num_kv_heads <= 0) return B200_ERR_RANGE;
+    if (num_tokens == 0) return B200_OK;
+    if (!q || !k || !v || !positions || !cos_sin_cache || !q_out || !k_cache || !v_cache || !slot_mapping)
+        return B200_ERR_NULL;                                       /* k_out and the weights may be NULL */
+    if (head_dim != B200_HD_CONST) return B200_ERR_SHAPE;
+    if (!aligned16(q) || !aligned16(k) || !aligned16(v) || !aligned16(q_out) || (k_out && !aligned16(k_out)) ||
+        !aligned16(k_cache) || !aligned16(v_cache) || !stride_ok(q_token_stride) || !stride_ok(k_token_stride) ||
+        !stride_ok(v_token_stride) || (reinterpret_cast<uintptr_t>(cos_sin_cache) & 15))
+        return B200_ERR_ALIGN;
+    return launch_qk_norm_rope_store(q, q_token_stride, k, k_token_stride, v, v_token_stride, positions, cos_sin_cache,
+                                     q_weight, k_weight, eps, q_out, k_out, k_cache, v_cache, slot_mapping,
+                                     num_tokens, num_heads, num_kv_heads, (cudaStream_t)stream);
 }
 
 int b200_rmsnorm(const void* x, void* residual, const void* weight, float eps, void* out,

@@ -20,6 +20,11 @@ int launch_kv_scatter_generic(const void* key, const void* value, int64_t key_ro
 int launch_qk_norm_rope(const void* q, int64_t q_token_stride, const void* k, int64_t k_token_stride,
                         const int64_t* positions, const float* cos_sin, const void* qw, const void* kw, float eps,
                         void* q_out, void* k_out, int32_t T, int32_t Hq, int32_t Hkv, cudaStream_t stream);
+int launch_qk_norm_rope_store(const void* q, int64_t q_token_stride, const void* k, int64_t k_token_stride,
+                              const void* v, int64_t v_token_stride,
+                              const int64_t* positions, const float* cos_sin, const void* qw, const void* kw, float eps,
+                              void* q_out, void* k_out, void* k_cache, void* v_cache, const int32_t* slot_mapping,
+                              int32_t T, int32_t Hq, int32_t Hkv, cudaStream_t stream);
 int launch_rmsnorm(const void* x, void* residual, const void* weight, float eps, void* out,
                    int32_t T, int32_t hidden, cudaStream_t stream);
 int launch_silu_and_mul(const void* x, void* out, int32_t T, int32_t inter, cudaStream_t stream);

@@ -38,29 +38,54 @@ __global__ void __launch_bounds__(256) kv_scatter_kernel(
 //      Roundings follow layernorm.py:85-93 and rotary_embedding.py:60-65 exactly:
 //      bf16(x*rstd), bf16(.*w), fp32 rotate (un-fused mul/sub), bf16.
 // ------------------------------------------------------------------------------------------
+// STORE = true additionally performs the KV scatter of piece (1) in the same launch:
+// rows are then (token, head) over Hq + 2*Hkv heads; a k row is written to k_out (if given) AND to
+// k_cache[slot], a v row is copied to v_cache[slot]; slot -1 skips the cache write (attention.py:79).
+struct KvStoreArgs {
+    const __nv_bfloat16* v; int64_t v_token_stride;
+    __nv_bfloat16* k_cache; __nv_bfloat16* v_cache; const int32_t* slot_mapping;
+};
+
+template <bool STORE>
 __global__ void __launch_bounds__(256) qk_norm_rope_kernel(
     const __nv_bfloat16* __restrict__ q, int64_t q_token_stride,
     const __nv_bfloat16* __restrict__ k, int64_t k_token_stride,
     const int64_t* __restrict__ positions, const float* __restrict__ cos_sin,
     const __nv_bfloat16* __restrict__ q_weight, const __nv_bfloat16* __restrict__ k_weight, float eps,
     __nv_bfloat16* __restrict__ q_out, __nv_bfloat16* __restrict__ k_out,
-    int64_t total_rows, int32_t Hq, int32_t Hkv) {
+    int64_t total_rows, int32_t Hq, int32_t Hkv, const KvStoreArgs st) {
     const int sub = threadIdx.x & 7;
     const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
     const bool live = row < total_rows;                        // dead lanes still take part in the shuffles
-    const int32_t H = Hq + Hkv;
+    const int32_t H = STORE ? Hq + 2 * Hkv : Hq + Hkv;
     const int64_t tok = live ? row / H : 0;
     const int32_t h = live ? (int32_t)(row - tok * H) : 0;
     const bool is_q = h < Hq;
+    const bool is_v = STORE && h >= Hq + Hkv;
     const __nv_bfloat16* src = is_q ? q + tok * q_token_stride + (int64_t)h * B200_HD
+                             : is_v ? st.v + tok * st.v_token_stride + (int64_t)(h - Hq - Hkv) * B200_HD
                                     : k + tok * k_token_stride + (int64_t)(h - Hq) * B200_HD;
-    __nv_bfloat16* dst = is_q ? q_out + (tok * Hq + h) * B200_HD : k_out + (tok * Hkv + (h - Hq)) * B200_HD;
+    __nv_bfloat16* dst = is_q ? q_out + (tok * Hq + h) * B200_HD
+                              : (k_out != nullptr ? k_out + (tok * Hkv + (h - Hq)) * B200_HD : nullptr);
     const __nv_bfloat16* w = is_q ? q_weight : k_weight;
+    __nv_bfloat16* cache_dst = nullptr;
+    if (STORE && live && !is_q) {
+        const int32_t slot = __ldg(st.slot_mapping + tok);
+        if (slot >= 0)
+            cache_dst = (is_v ? st.v_cache + (int64_t)(h - Hq - Hkv) * B200_HD : st.k_cache + (int64_t)(h - Hq) * B200_HD)
+                        + (int64_t)slot * Hkv * B200_HD;
+    }
 
     int4 lo4 = make_int4(0, 0, 0, 0), hi4 = lo4;
     if (live) {
         lo4 = ld_nc_v4(src + 8 * sub);
         hi4 = ld_nc_v4(src + 64 + 8 * sub);
+    }
+    if (STORE && is_v) {                                       // v is copied untouched (no shuffles below need it:
+        if (cache_dst != nullptr) {                            //  the butterfly stays inside an 8-lane row group,
+            st_v4(cache_dst + 8 * sub, lo4);                   //  but every lane must still execute it)
+            st_v4(cache_dst + 64 + 8 * sub, hi4);
+        }
     }
     const uint32_t lo_u[4] = {(uint32_t)lo4.x, (uint32_t)lo4.y, (uint32_t)lo4.z, (uint32_t)lo4.w};
     const uint32_t hi_u[4] = {(uint32_t)hi4.x, (uint32_t)hi4.y, (uint32_t)hi4.z, (uint32_t)hi4.w};
@@ -94,7 +119,7 @@ __global__ void __launch_bounds__(256) qk_norm_rope_kernel(
             x2[2 * j] = nrm(x2[2 * j], b.x); x2[2 * j + 1] = nrm(x2[2 * j + 1], b.y);
         }
     }
-    if (!live) return;
+    if (!live || is_v) return;
     const float* cs = cos_sin + positions[tok] * B200_HD + 8 * sub;       // [cos(64) | sin(64)]
     const float4 c0 = *reinterpret_cast<const float4*>(cs), c1 = *reinterpret_cast<const float4*>(cs + 4);
     const float4 s0 = *reinterpret_cast<const float4*>(cs + 64), s1 = *reinterpret_cast<const float4*>(cs + 68);
@@ -110,8 +135,15 @@ __global__ void __launch_bounds__(256) qk_norm_rope_kernel(
         y2[j] = pack_bf16x2(__fadd_rn(__fmul_rn(x2[a], c[a]), __fmul_rn(x1[a], s[a])),
                             __fadd_rn(__fmul_rn(x2[b], c[b]), __fmul_rn(x1[b], s[b])));
     }
-    st_v4(dst + 8 * sub, make_int4(y1[0], y1[1], y1[2], y1[3]));
-    st_v4(dst + 64 + 8 * sub, make_int4(y2[0], y2[1], y2[2], y2[3]));
+    const int4 o_lo = make_int4(y1[0], y1[1], y1[2], y1[3]), o_hi = make_int4(y2[0], y2[1], y2[2], y2[3]);
+    if (dst != nullptr) {
+        st_v4(dst + 8 * sub, o_lo);
+        st_v4(dst + 64 + 8 * sub, o_hi);
+    }
+    if (STORE && cache_dst != nullptr) {
+        st_v4(cache_dst + 8 * sub, o_lo);
+        st_v4(cache_dst + 64 + 8 * sub, o_hi);
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -274,10 +306,27 @@ int launch_qk_norm_rope(const void* q, int64_t q_token_stride, const void* k, in
                         void* q_out, void* k_out, int32_t T, int32_t Hq, int32_t Hkv, cudaStream_t stream) {
     const int64_t rows = (int64_t)T * (Hq + Hkv);
     const int64_t blocks = (rows + 31) / 32;                      // 8 lanes per row, 256 threads
-    qk_norm_rope_kernel<<<(unsigned)blocks, 256, 0, stream>>>(
+    qk_norm_rope_kernel<false><<<(unsigned)blocks, 256, 0, stream>>>(
         (const __nv_bfloat16*)q, q_token_stride, (const __nv_bfloat16*)k, k_token_stride, positions, cos_sin,
         (const __nv_bfloat16*)qw, (const __nv_bfloat16*)kw, eps, (__nv_bfloat16*)q_out, (__nv_bfloat16*)k_out,
-        rows, Hq, Hkv);
+        rows, Hq, Hkv, KvStoreArgs{});
+    return (int)cudaGetLastError();
+}
+
+int launch_qk_norm_rope_store(const void* q, int64_t q_token_stride, const void* k, int64_t k_token_stride,
+                              const void* v, int64_t v_token_stride,
+                              const int64_t* positions, const float* cos_sin, const void* qw, const void* kw, float eps,
+                              void* q_out, void* k_out, void* k_cache, void* v_cache, const int32_t* slot_mapping,
+                              int32_t T, int32_t Hq, int32_t Hkv, cudaStream_t stream) {
+    const int64_t rows = (int64_t)T * (Hq + 2 * Hkv);
+    const int64_t blocks = (rows + 31) / 32;
+    KvStoreArgs st;
+    st.v = (const __nv_bfloat16*)v; st.v_token_stride = v_token_stride;
+    st.k_cache = (__nv_bfloat16*)k_cache; st.v_cache = (__nv_bfloat16*)v_cache; st.slot_mapping = slot_mapping;
+    qk_norm_rope_kernel<true><<<(unsigned)blocks, 256, 0, stream>>>(
+        (const __nv_bfloat16*)q, q_token_stride, (const __nv_bfloat16*)k, k_token_stride, positions, cos_sin,
+        (const __nv_bfloat16*)qw, (const __nv_bfloat16*)kw, eps, (__nv_bfloat16*)q_out, (__nv_bfloat16*)k_out,
+        rows, Hq, Hkv, st);
     return (int)cudaGetLastError();
 }
 

@@ -409,3 +409,38 @@ def test_rotation_only_and_large_shapes(ops):
     h = torch.randn(300, 5120, generator=g).bfloat16()
     w = (1 + 0.1 * torch.randn(5120, generator=g)).bfloat16()
     assert _ulp_ok(ops.rms_norm(h.cuda(), w.cuda(), 1e-6), oracle.rms_norm(h, w))
+
+
+@pytest.mark.parametrize("Hq,Hkv,T,need_k", [(16, 8, 300, True), (32, 8, 513, False), (8, 1, 77, True), (5, 1, 1, True)])
+def test_fused_norm_rope_store_equals_unfused_then_scatter(ops, Hq, Hkv, T, need_k):
+    """one launch = qk_norm_rope (4a) + kv_scatter (1).  q'/k' must carry the same bits as the
+    unfused kernel (which is held to the oracle above) and the caches the same bits as the oracle's scatter
+    of (k', v) -- including rows with slot -1 left untouched."""
+    g = torch.Generator().manual_seed(100 + T)
+    D, P, nblk = 128, 256, 6
+    qkv = torch.randn(T, (Hq + 2 * Hkv) * D, generator=g).bfloat16()
+    pos = torch.randint(0, 40960, (T,), generator=g)
+    wq = (1 + 0.1 * torch.randn(D, generator=g)).bfloat16()
+    wk = (1 + 0.1 * torch.randn(D, generator=g)).bfloat16()
+    cache = oracle.make_cos_sin_cache(D, 40960, 1e6).view(-1, D)
+    slots = torch.randperm(nblk * P, generator=g)[:T].to(torch.int32)
+    slots[::7] = -1
+    kc0 = torch.randn(nblk, P, Hkv, D, generator=g).bfloat16()
+    vc0 = torch.randn(nblk, P, Hkv, D, generator=g).bfloat16()
+    qkv_d = qkv.cuda()
+    qd, kd, vd = (t.view(T, -1, D) for t in qkv_d.split([Hq * D, Hkv * D, Hkv * D], dim=-1))
+    q_ref, k_ref = ops.qk_norm_rope(qd, kd, pos.cuda(), wq.cuda(), wk.cuda(), cache.cuda(), 1e-6)
+    kc_want, vc_want = kc0.clone(), vc0.clone()
+    oracle.kv_scatter(k_ref.cpu(), vd.cpu(), kc_want, vc_want, slots)
+    kc, vc = kc0.cuda(), vc0.cuda()
+    q_got, k_got = ops.qk_norm_rope_store(qd, kd, vd, pos.cuda(), wq.cuda(), wk.cuda(), cache.cuda(), 1e-6,
+                                          kc, vc, slots.cuda(), need_k_out=need_k)
+    assert torch.equal(q_got, q_ref)
+    assert (k_got is None) == (not need_k)
+    if need_k:
+        assert torch.equal(k_got, k_ref)
+    assert torch.equal(kc.cpu(), kc_want) and torch.equal(vc.cpu(), vc_want)
+    # rotation-only form (qkv_bias models): NULL weights
+    q2, k2 = ops.qk_norm_rope_store(qd, kd, vd, pos.cuda(), None, None, cache.cuda(), 1e-6, kc, vc, slots.cuda())
+    q2r, k2r = ops.qk_norm_rope(qd, kd, pos.cuda(), None, None, cache.cuda())
+    assert torch.equal(q2, q2r) and torch.equal(k2, k2r)

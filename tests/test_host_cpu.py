@@ -72,6 +72,7 @@ def test_install_patches_reference_classes_in_place():
         assert att.store_kvcache is ops.store_kvcache
         mr = importlib.import_module("nanovllm.engine.model_runner")
         assert mr.ModelRunner.prepare_model_input.__module__ == "b200attn.install"
+        assert mr.ModelRunner.run.__module__ == "b200attn.install"
         # CPU tensors must be refused, not silently computed (no CPU fallback on the product path)
         from nanovllm.utils.context import reset_context, set_context
         set_context(torch.tensor([0, 2], dtype=torch.int32), torch.tensor([0, 2], dtype=torch.int32), 2, 2,
@@ -82,3 +83,45 @@ def test_install_patches_reference_classes_in_place():
         reset_context()
     finally:
         sys.path.remove(REF)
+
+
+def test_run_returns_host_indices_for_the_untouched_postprocess():
+    """ours.run keeps ModelRunner.run's pipeline and return shape (model_runner.py:602-638) but hands
+    Scheduler.postprocess (scheduler.py:247-250) the indices as a host list: same values, same order,
+    len() and zip() behave, and an index is usable as `seqs[i]`."""
+    from types import SimpleNamespace
+    from b200attn.engine import model_runner as ours
+    calls = []
+
+    class FakeRunner:
+        rank = 0
+
+        def prepare_model_input(self, seqs):
+            self._b200_need_logits_host = [0, 2]
+            calls.append("prepare")
+            return torch.zeros(3, dtype=torch.int64), torch.zeros(3, dtype=torch.int64)
+
+        def prepare_sample(self, seqs):
+            calls.append("sample_prep")
+            return torch.ones(2)
+
+        def run_model(self, ids, pos):
+            calls.append("forward")
+            return torch.zeros(2, 8)
+
+        def sampler(self, logits, temps):
+            calls.append("sampler")
+            return torch.tensor([7, 9])
+
+    ctx = SimpleNamespace(seq_need_compute_logits=torch.tensor([0, 2], dtype=torch.int32))
+    reset = []
+    toks, need = ours.run(FakeRunner(), ["a", "b", "c"], lambda: ctx, lambda: reset.append(1))
+    assert calls == ["prepare", "sample_prep", "forward", "sampler"] and reset == [1]
+    assert toks == [7, 9] and need == [0, 2] and isinstance(need, list)
+    assert [["a", "b", "c"][i] for i, _ in zip(need, toks)] == ["a", "c"]
+
+    class ForeignPrepare(FakeRunner):                      # someone else's prepare_model_input: fall back to the Context
+        def prepare_model_input(self, seqs):
+            return torch.zeros(3, dtype=torch.int64), torch.zeros(3, dtype=torch.int64)
+    _, need2 = ours.run(ForeignPrepare(), ["a", "b", "c"], lambda: ctx, lambda: None)
+    assert need2 is ctx.seq_need_compute_logits

@@ -11,6 +11,10 @@ gets the same harness patches, applied identically to BOTH arms (reference and d
                               of the other arm's run (teacher forcing), so every decision of the two
                               arms is taken on an identical context
   B200E2E_SHM_BYTES=<n>       size of the rank-0 -> worker shared-memory mailbox (F11)
+  B200E2E_STEP_PROFILE=<json> rank 0: wall time of every phase of every engine step (schedule,
+                              prepare_model_input, forward with a device sync either side, sampler +
+                              .tolist(), postprocess) -- perturbs throughput, so never combined with a
+                              tok/s measurement
 
 and then chains to the product hook nano-vllm-v1_b200/dropin/sitecustomize.py (B200ATTN_DROPIN)."""
 import atexit
@@ -89,6 +93,9 @@ def _patch(module):
                     with open(out, "w") as f:
                         json.dump({str(k): v for k, v in _PER_SEQ.items()}, f)
             atexit.register(dump)
+    prof_out = os.environ.get("B200E2E_STEP_PROFILE")
+    if prof_out:
+        _install_step_profile(module, prof_out)
     shm = os.environ.get("B200E2E_SHM_BYTES")
     if shm:
         real = module.SharedMemory
@@ -96,6 +103,74 @@ def _patch(module):
         def bigger(name=None, create=False, size=0):
             return real(name=name, create=create, size=int(shm) if create else size)
         module.SharedMemory = bigger
+
+
+def _install_step_profile(module, out_path):
+    import time
+    import torch
+    sched = importlib.import_module("nanovllm.engine.scheduler")
+    steps, cur = [], {}
+
+    def timed(cls, name, key, sync=False):
+        orig = getattr(cls, name)
+
+        def wrapper(self, *a, **kw):
+            if sync:
+                torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            try:
+                return orig(self, *a, **kw)
+            finally:
+                if sync:
+                    torch.cuda.synchronize()
+                cur[key] = cur.get(key, 0.0) + time.perf_counter() - t0
+        setattr(cls, name, wrapper)
+
+    kern_out = os.environ.get("B200E2E_KERNEL_PROFILE")
+    if kern_out:
+        # CUPTI kernel table of a few mid-run decode steps (graph replays): which kernels the step is made of
+        orig_rm = module.ModelRunner.run_model
+        calls = {"n": 0}
+        first = int(os.environ.get("B200E2E_KERNEL_PROFILE_STEP", "120"))
+
+        def run_model(self, input_ids, positions):
+            calls["n"] += 1
+            if self.rank != 0 or not (first <= calls["n"] < first + 4):
+                return orig_rm(self, input_ids, positions)
+            from torch.profiler import ProfilerActivity, profile
+            torch.cuda.synchronize()
+            with profile(activities=[ProfilerActivity.CUDA]) as prof:
+                out = orig_rm(self, input_ids, positions)
+                torch.cuda.synchronize()
+            rows = [dict(name=e.key, calls=e.count, cuda_us=e.device_time_total) for e in prof.key_averages()]
+            rows.sort(key=lambda r: -r["cuda_us"])
+            with open(f"{kern_out}.{calls['n']}.json", "w") as f:
+                json.dump(dict(tokens=int(input_ids.numel()), rows=rows), f)
+            return out
+        module.ModelRunner.run_model = run_model
+    timed(module.ModelRunner, "prepare_model_input", "prepare")
+    timed(module.ModelRunner, "run_model", "forward_synced", sync=True)
+    timed(module.ModelRunner, "run", "run_total")
+    timed(sched.Scheduler, "schedule", "schedule")
+    orig_post = sched.Scheduler.postprocess
+
+    def post(self, seqs, token_ids, need):
+        t0 = time.perf_counter()
+        try:
+            return orig_post(self, seqs, token_ids, need)
+        finally:
+            cur["postprocess"] = time.perf_counter() - t0
+            cur["num_seqs"] = len(seqs)
+            cur["t_end"] = time.perf_counter()
+            steps.append(dict(cur))
+            cur.clear()
+    sched.Scheduler.postprocess = post
+
+    def dump():
+        if steps:
+            with open(out_path, "w") as f:
+                json.dump(steps, f)
+    atexit.register(dump)
 
 
 class _Loader(importlib.abc.Loader):
@@ -127,5 +202,5 @@ _product = os.path.join(os.path.dirname(os.path.dirname(os.path.dirname(os.path.
                         "nano-vllm-v1_b200", "dropin", "sitecustomize.py")
 if os.environ.get("B200ATTN_DROPIN") and os.path.exists(_product):
     runpy.run_path(_product)                         # product hook first ...
-if _SEED is not None or _GREEDY or os.environ.get("B200E2E_SHM_BYTES"):
+if _SEED is not None or _GREEDY or os.environ.get("B200E2E_SHM_BYTES") or os.environ.get("B200E2E_STEP_PROFILE"):
     sys.meta_path.insert(0, _Finder())               # ... so the harness finder sits in front and wraps it

@@ -34,6 +34,10 @@ def launcher(a):
         env["B200ATTN_DROPIN"] = "1"
     elif a.arm == "dropin-attn":
         env["B200ATTN_DROPIN"] = "attn"
+    if a.step_profile:
+        env["B200E2E_STEP_PROFILE"] = os.path.abspath(a.step_profile)
+        if a.kernel_profile:
+            env["B200E2E_KERNEL_PROFILE"] = os.path.abspath(a.kernel_profile)
     if a.greedy:
         env["B200E2E_GREEDY"] = "1"
         env["B200E2E_MARGINS_OUT"] = a.out + ".margins"
@@ -156,6 +160,8 @@ def main():
     ap.add_argument("--tie-margin", type=float, default=0.032, help="2 bf16 ulps at |logit| in [2,4)")
     ap.add_argument("--force-tokens", default=None, help="JSON of the other arm's greedy run to teacher-force")
     ap.add_argument("--repeat", type=int, default=2)
+    ap.add_argument("--kernel-profile", default=None, help="with --step-profile: CUPTI kernel table of 4 decode steps (prefix)")
+    ap.add_argument("--step-profile", default=None, help="write per-step phase timings here (perturbs tok/s)")
     a = ap.parse_args()
     if a.compare:
         v = compare(a.compare[0], a.compare[1], a.steps, a.tie_margin)
