@@ -56,10 +56,13 @@ class _Staging:
         if self.events[i] is not None:
             self.events[i].synchronize()
         if self.bufs[i] is None or self.bufs[i].numel() < nbytes:
-            self.bufs[i] = torch.empty(max(nbytes * 2, 1 << 16), dtype=torch.uint8, device="cpu", pin_memory=True)
+            self.bufs[i] = torch.empty(max(nbytes * 2, 1 << 16), dtype=torch.uint8, device="cpu",
+                                       pin_memory=torch.cuda.is_available())
         return self.bufs[i]
 
     def sent(self):
+        if not torch.cuda.is_available():
+            return
         ev = torch.cuda.Event()
         ev.record()
         self.events[self.turn] = ev
@@ -116,39 +119,59 @@ _ORDER = ("input_ids", "positions", "cu_seqlens_q", "cu_seqlens_k", "slot_mappin
           "seq_need_compute_logits", "block_tables")
 
 
-def prepare_model_input(self, seqs, _set_context):
-    arrays, max_q, max_k = build_model_input(seqs, self.block_size)
+def _layout_of(arrays):
+    """[(name, offset, nbytes, dtype_char, shape)] for the non-None arrays, 16-byte aligned offsets."""
+    layout, nbytes = [], 0
+    for name in _ORDER:
+        a = arrays[name]
+        if a is None:
+            continue
+        layout.append((name, nbytes, a.nbytes, "q" if a.dtype == np.int64 else "i", tuple(a.shape)))
+        nbytes += (a.nbytes + _ALIGN - 1) // _ALIGN * _ALIGN
+    return layout, max(nbytes, _ALIGN)
+
+
+def _staging_of(self):
     staging = getattr(self, "_b200_staging", None)
     if staging is None:
         staging = self._b200_staging = _Staging()
-    offs, nbytes = {}, 0
-    for name in _ORDER:
-        a = arrays[name]
-        if a is None:
-            continue
-        offs[name] = nbytes
-        nbytes += (a.nbytes + _ALIGN - 1) // _ALIGN * _ALIGN
-    host = staging.get(max(nbytes, _ALIGN))
+    return staging
+
+
+def _pack(self, arrays):
+    """Arrays -> one pinned host arena (returns its layout and the pinned uint8 tensor)."""
+    layout, nbytes = _layout_of(arrays)
+    host = _staging_of(self).get(nbytes)
     host_np = host.numpy()
-    for name, off in offs.items():
-        a = arrays[name]
-        host_np[off:off + a.nbytes] = a.reshape(-1).view(np.uint8)
-    dev = torch.empty(max(nbytes, _ALIGN), dtype=torch.uint8, device="cuda")
-    dev.copy_(host[:max(nbytes, _ALIGN)], non_blocking=True)
-    staging.sent()
-    out = {}
-    for name in _ORDER:
-        a = arrays[name]
-        if a is None:
-            out[name] = None
-            continue
-        dt = torch.int64 if a.dtype == np.int64 else torch.int32
-        out[name] = dev[offs[name]:offs[name] + a.nbytes].view(dt).view(a.shape)
-    self._b200_need_logits_host = arrays["seq_need_compute_logits"].tolist()
+    for name, off, nb, _, _ in layout:
+        host_np[off:off + nb] = arrays[name].reshape(-1).view(np.uint8)
+    return layout, nbytes, host
+
+
+def _upload_and_set_context(self, layout, nbytes, host, max_q, max_k, _set_context):
+    """ONE H2D copy of the packed arena, then the eight Context fields as views of it."""
+    dev = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    dev.copy_(host[:nbytes], non_blocking=True)
+    _staging_of(self).sent()
+    out = dict.fromkeys(_ORDER)
+    for name, off, nb, ch, shape in layout:
+        out[name] = dev[off:off + nb].view(torch.int64 if ch == "q" else torch.int32).view(shape)
     _set_context(out["cu_seqlens_q"], out["cu_seqlens_k"], max_q, max_k, out["slot_mapping"], out["context_lens"],
                  out["block_tables"], out["seq_need_compute_logits"])
     return out["input_ids"], out["positions"]
 
+
+def prepare_model_input(self, seqs, _set_context):
+    pre = getattr(self, "_b200_prebuilt", None)
+    if pre is not None and pre[0] is seqs:                 # rank 0 under TP: `call` already built and packed this step
+        _, layout, nbytes, host, max_q, max_k, need = pre
+        self._b200_prebuilt = None
+    else:
+        arrays, max_q, max_k = build_model_input(seqs, self.block_size)
+        layout, nbytes, host = _pack(self, arrays)
+        need = arrays["seq_need_compute_logits"].tolist()
+    self._b200_need_logits_host = need
+    return _upload_and_set_context(self, layout, nbytes, host, max_q, max_k, _set_context)
 
 def run(self, seqs, _get_context, _reset_context):
     """ModelRunner.run (model_runner.py:602-638): prepare -> forward -> sample; see module docstring."""
@@ -162,3 +185,37 @@ def run(self, seqs, _get_context, _reset_context):
         need = _get_context().seq_need_compute_logits
     _reset_context()
     return token_ids, need
+
+
+# ---- tensor-parallel control plane (model_runner.py:241-288) ---------------------------
+# The reference pickles the scheduled `Sequence` objects -- every token id of every sequence -- into the
+# shared-memory mailbox on every step, and each worker unpickles them and re-runs prepare_model_input.
+# All a worker needs is the packed metadata arena rank 0 builds anyway, so rank 0 sends THAT (one bytes
+# object + a tiny layout) as a "run_packed" call; workers upload it and run the forward.  Message
+# format, mailbox, events and the `loop`/`read_shm`/`write_shm` methods are the reference's, untouched.
+_MAILBOX_HEADROOM = 4096
+
+
+def call(self, method_name, *args, _reference_call=None):
+    if method_name == "run" and self.world_size > 1 and self.rank == 0 and len(args) == 1:
+        seqs = args[0]
+        arrays, max_q, max_k = build_model_input(seqs, self.block_size)
+        layout, nbytes, host = _pack(self, arrays)
+        if nbytes + _MAILBOX_HEADROOM <= self.shm.size:
+            self.write_shm("run_packed", layout, nbytes, max_q, max_k, host.numpy()[:nbytes].tobytes())
+            self._b200_prebuilt = (seqs, layout, nbytes, host, max_q, max_k, arrays["seq_need_compute_logits"].tolist())
+            return self.run(seqs)
+        # too large for the mailbox: the reference's own message (it would overflow there as well)
+        self._b200_prebuilt = (seqs, layout, nbytes, host, max_q, max_k, arrays["seq_need_compute_logits"].tolist())
+    return _reference_call(self, method_name, *args)
+
+
+def run_packed(self, layout, nbytes, max_q, max_k, payload, _set_context, _reset_context):
+    """Worker side of `call("run", seqs)`: same forward as ModelRunner.run on rank > 0 (no sampling there,
+    model_runner.py:631-633), fed from rank 0's packed arena instead of re-deriving it from Sequences."""
+    host = _staging_of(self).get(nbytes)
+    host.numpy()[:nbytes] = np.frombuffer(payload, dtype=np.uint8, count=nbytes)
+    input_ids, positions = _upload_and_set_context(self, layout, nbytes, host, max_q, max_k, _set_context)
+    self.run_model(input_ids, positions)
+    _reset_context()
+    return None

@@ -12,7 +12,7 @@ stay valid whatever was imported first:
     nanovllm.layers.layernorm.RMSNorm.forward          -> b200_rmsnorm (fused residual add)
     nanovllm.layers.rotary_embedding.RotaryEmbedding.forward -> rotation-only kernel
     nanovllm.layers.activation.SiluAndMul.forward      -> b200_silu_and_mul
-    nanovllm.engine.model_runner.ModelRunner.{allocate_kv_cache, prepare_model_input, run}
+    nanovllm.engine.model_runner.ModelRunner.{allocate_kv_cache, prepare_model_input, run, call, run_packed}
 
 `LLM.generate`, `Scheduler`, `BlockManager`, `Sequence`, the linears, the sampler and NCCL are untouched.
 `install(pointwise=False)` limits the patch to attention + scatter; `install(runner=False)`
@@ -94,6 +94,10 @@ def install(pointwise: bool = True, runner: bool = True) -> None:
         mr.ModelRunner.allocate_kv_cache = lambda self: ours.allocate_kv_cache(self, ref_alloc)
         mr.ModelRunner.prepare_model_input = lambda self, seqs: ours.prepare_model_input(self, seqs, ctx.set_context)
         mr.ModelRunner.run = lambda self, seqs: ours.run(self, seqs, ctx.get_context, ctx.reset_context)
+        ref_call = mr.ModelRunner.call
+        mr.ModelRunner.call = lambda self, method_name, *args: ours.call(self, method_name, *args, _reference_call=ref_call)
+        mr.ModelRunner.run_packed = lambda self, layout, nbytes, max_q, max_k, payload: ours.run_packed(
+            self, layout, nbytes, max_q, max_k, payload, ctx.set_context, ctx.reset_context)
     _INSTALLED = True
 
 

@@ -125,3 +125,71 @@ def test_run_returns_host_indices_for_the_untouched_postprocess():
             return torch.zeros(3, dtype=torch.int64), torch.zeros(3, dtype=torch.int64)
     _, need2 = ours.run(ForeignPrepare(), ["a", "b", "c"], lambda: ctx, lambda: None)
     assert need2 is ctx.seq_need_compute_logits
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "prepare_*.pt"))))
+def test_tp_control_plane_ships_the_packed_arena(path, monkeypatch):
+    """under TP rank 0 sends ("run_packed", layout, nbytes, max_q, max_k, bytes) through the
+    reference's own mailbox instead of pickled Sequences.  Round-trip the message through pickle (as
+    write_shm/read_shm do, model_runner.py:212-264) and check that the worker sets a Context with exactly
+    the values the reference's prepare_model_input produces (the golden fixtures)."""
+    import pickle
+    from b200attn.engine import model_runner as ours
+    m = torch.load(path)
+    seqs = [_Seq(s) for s in m["states"]]
+    sent, ran = [], []
+
+    class Rank0:
+        world_size, rank, block_size = 2, 0, 256
+        shm = type("Shm", (), {"size": 1 << 20})()
+
+        def write_shm(self, method_name, *args):
+            sent.append(pickle.dumps([method_name, *args]))
+
+        def run(self, s):
+            ran.append(s)
+            return "tokens"
+
+    r0 = Rank0()
+    assert ours.call(r0, "run", seqs, _reference_call=None) == "tokens" and ran == [seqs]
+    assert r0._b200_prebuilt[0] is seqs                       # rank 0 reuses the arena it just packed
+    method, *args = pickle.loads(sent[0])
+    assert method == "run_packed" and len(sent[0]) < 1 << 20
+
+    got = {}
+
+    def fake_upload(self, layout, nbytes, host, max_q, max_k, _set_context):
+        raw = host.numpy()[:nbytes]
+        for name, off, nb, ch, shape in layout:
+            dt = torch.int64 if ch == "q" else torch.int32
+            got[name] = torch.from_numpy(raw[off:off + nb].copy()).view(dt).view(shape) if nb else torch.zeros(shape, dtype=dt)
+        got["max_q"], got["max_k"] = max_q, max_k
+        return got["input_ids"], got["positions"]
+    monkeypatch.setattr(ours, "_upload_and_set_context", fake_upload)
+
+    class Worker:
+        world_size, rank = 2, 1
+        forwards = []
+
+        def run_model(self, ids, pos):
+            self.forwards.append((ids, pos))
+
+    w = Worker()
+    assert ours.run_packed(w, *args, _set_context=None, _reset_context=lambda: None) is None
+    assert len(w.forwards) == 1
+    assert got["max_q"] == m["max_seqlen_q"] and got["max_k"] == m["max_seqlen_k"]
+    for name in ("input_ids", "positions", "cu_seqlens_q", "cu_seqlens_k", "slot_mapping", "context_lens",
+                 "seq_need_compute_logits", "block_tables"):
+        if m[name] is None:
+            assert name not in got, name
+        else:
+            assert got[name].dtype == m[name].dtype and torch.equal(got[name], m[name]), name
+
+    # a step too large for the mailbox falls back to the reference's own message
+    r0.shm.size = 64
+    fell = []
+    ours.call(r0, "run", seqs, _reference_call=lambda self, name, *a: fell.append(name))
+    assert fell == ["run"] and len(sent) == 1
+    # other methods are forwarded untouched
+    ours.call(r0, "exit", _reference_call=lambda self, name, *a: fell.append(name))
+    assert fell == ["run", "exit"]
