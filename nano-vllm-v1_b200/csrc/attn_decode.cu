@@ -13,18 +13,23 @@
 //
 // Replaces flash_attn_with_kvcache (attention.py:229-232) and the q_len==1 case of
 // flash_attn_varlen_func (attention.py:242-248).
+#include <stdlib.h>
+#include <string.h>
+
 #include "common.cuh"
 #include "launch.h"
 
 namespace b200 {
 
-constexpr int DEC_WARPS = 4;
-constexpr int DEC_THREADS = DEC_WARPS * 32;
+// Two CTA shapes, same math (template parameters of the kernel):
+//   <4 warps, 3 stages>  96 KB, 2 CTAs/SM: 192 KB of loads in flight per SM, long contexts;
+//   <2 warps, 3 stages>  48 KB, 4 CTAs/SM: short contexts / many small CTAs, where what limits the SM
+//                        is the number of CTAs whose prologue (length -> block id -> first K bytes) and
+//                        merge epilogue can overlap, not the bytes in flight.
 constexpr int DEC_TOK = 16;                            // tokens per warp step
-constexpr int DEC_STAGES = 3;
 constexpr int DEC_TILE_BYTES = DEC_TOK * B200_HD * 2;  // 4 KB (K) ; same for V
 constexpr int DEC_STAGE_BYTES = 2 * DEC_TILE_BYTES;    // 8 KB
-constexpr int DEC_SMEM_BYTES = DEC_WARPS * DEC_STAGES * DEC_STAGE_BYTES;   // 96 KB -> 2 CTAs / SM
+constexpr int dec_smem_bytes(int warps, int stages) { return warps * stages * DEC_STAGE_BYTES; }
 constexpr int DEC_MIN_SPLIT_TOKENS = 256;              // never split finer than one page
 constexpr int DEC_CHUNKS_PER_PAGE = B200_PAGE / DEC_TOK;
 
@@ -61,7 +66,9 @@ __device__ __forceinline__ DecodeRow decode_row(const DecodeParams& p, int idx) 
     return r;
 }
 
-__global__ void __launch_bounds__(DEC_THREADS, 2) paged_decode_kernel(const DecodeParams p) {
+template <int DEC_WARPS, int DEC_STAGES, int MIN_CTAS>
+__global__ void __launch_bounds__(DEC_WARPS * 32, MIN_CTAS) paged_decode_kernel(const DecodeParams p) {
+    constexpr int DEC_THREADS = DEC_WARPS * 32;
     extern __shared__ __align__(1024) uint8_t smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int S = p.num_splits;
@@ -84,7 +91,8 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) paged_decode_kernel(const Deco
     if (c_begin >= c_end) {                                   // empty split or padding row (len 0)
         if (S == 1) {
             for (int r = 0; r < G; ++r)
-                p.out[tok * p.out_token_stride + (int64_t)(h * G + r) * B200_HD + threadIdx.x] = __float2bfloat16(0.f);
+                for (int t = threadIdx.x; t < B200_HD; t += DEC_THREADS)
+                    p.out[tok * p.out_token_stride + (int64_t)(h * G + r) * B200_HD + t] = __float2bfloat16(0.f);
         } else if (threadIdx.x < G) {
             p.ws_lse[((int64_t)bi * S + s) * p.Hq + h * G + threadIdx.x] = -INFINITY;
         }
@@ -233,8 +241,8 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) paged_decode_kernel(const Deco
         if (r1 < G) *reinterpret_cast<float2*>(sm_o + (warp * 16 + r1) * B200_HD + nt * 8 + cq) = make_float2(o[nt][2], o[nt][3]);
     }
     __syncthreads();
-    const int t = threadIdx.x;                                    // one thread per head-dim element
-    for (int r = 0; r < G; ++r) {
+    for (int idx = threadIdx.x; idx < G * B200_HD; idx += DEC_THREADS) {   // one thread per (head, head-dim element)
+        const int r = idx >> 7, t = idx & (B200_HD - 1);
         float ms = -INFINITY;
 #pragma unroll
         for (int w = 0; w < DEC_WARPS; ++w) ms = fmaxf(ms, sm_m[w * 16 + r]);
@@ -250,9 +258,9 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) paged_decode_kernel(const Deco
         if (S == 1) {
             p.out[tok * p.out_token_stride + (int64_t)head * B200_HD + t] = __float2bfloat16_rn(val);
         } else {
-            const int64_t idx = ((int64_t)bi * S + s) * p.Hq + head;
-            p.ws_o[idx * B200_HD + t] = val;
-            if (t == 0) p.ws_lse[idx] = ms + log2f(den);
+            const int64_t widx = ((int64_t)bi * S + s) * p.Hq + head;
+            p.ws_o[widx * B200_HD + t] = val;
+            if (t == 0) p.ws_lse[widx] = ms + log2f(den);
         }
     }
 }
@@ -281,13 +289,38 @@ __global__ void __launch_bounds__(B200_HD) decode_reduce_kernel(const DecodePara
     p.out[(int64_t)row.tok * p.out_token_stride + (int64_t)head * B200_HD + t] = __float2bfloat16_rn(val);
 }
 
-int launch_attn_decode(const DecodeArgs& a, cudaStream_t stream) {
+template <int W, int ST, int MC>
+static int launch_decode_shape(const DecodeParams& p, int64_t grid, cudaStream_t stream) {
     static bool attr_set = false;
+    constexpr int SMEM = dec_smem_bytes(W, ST);
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(paged_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_SMEM_BYTES);
+        cudaError_t e = cudaFuncSetAttribute(paged_decode_kernel<W, ST, MC>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
         if (e != cudaSuccess) return (int)e;
         attr_set = true;
     }
+    paged_decode_kernel<W, ST, MC><<<(unsigned)grid, W * 32, SMEM, stream>>>(p);
+    return (int)cudaGetLastError();
+}
+
+// CTA shape of a launch: host-only (static under CUDA graphs).  B200ATTN_DECODE_SHAPE=w4s3|w2s3|w4s2|w2s2 overrides.
+int decode_shape(int64_t grid_ctas) {
+    static int forced = -2;
+    if (forced == -2) {
+        const char* env = getenv("B200ATTN_DECODE_SHAPE");
+        forced = -1;
+        if (env) {
+            if (!strcmp(env, "w4s3")) forced = 0;
+            else if (!strcmp(env, "w2s3")) forced = 1;
+            else if (!strcmp(env, "w4s2")) forced = 2;
+            else if (!strcmp(env, "w2s2")) forced = 3;
+        }
+    }
+    if (forced >= 0) return forced;
+    (void)grid_ctas;
+    return 0;
+}
+
+int launch_attn_decode(const DecodeArgs& a, cudaStream_t stream) {
     DecodeParams p;
     p.q = (const __nv_bfloat16*)a.q; p.q_token_stride = a.q_token_stride;
     p.k_cache = (const uint8_t*)a.k_cache; p.v_cache = (const uint8_t*)a.v_cache;
@@ -299,9 +332,15 @@ int launch_attn_decode(const DecodeArgs& a, cudaStream_t stream) {
     p.cu_q = a.cu_q; p.cu_k = a.cu_k; p.row_list = a.row_list; p.n_rows = a.n_rows;
     if (a.batch == 0) return 0;
     const int64_t grid = (int64_t)a.batch * a.Hkv * a.num_splits;
-    paged_decode_kernel<<<(unsigned)grid, DEC_THREADS, DEC_SMEM_BYTES, stream>>>(p);
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) return (int)e;
+    int rc;
+    switch (decode_shape(grid)) {
+        case 1: rc = launch_decode_shape<2, 3, 4>(p, grid, stream); break;
+        case 2: rc = launch_decode_shape<4, 2, 2>(p, grid, stream); break;
+        case 3: rc = launch_decode_shape<2, 2, 5>(p, grid, stream); break;
+        default: rc = launch_decode_shape<4, 3, 2>(p, grid, stream); break;
+    }
+    if (rc != 0) return rc;
+    cudaError_t e = cudaSuccess;
     if (a.num_splits > 1) {
         decode_reduce_kernel<<<(unsigned)(a.batch * a.Hq), B200_HD, 0, stream>>>(p, a.batch);
         e = cudaGetLastError();

@@ -64,7 +64,19 @@ def decode_case(name, B, ctx, Hq, Hkv, iters, results, ragged=False):
     flush = torch.zeros(256 * 1024 * 1024 // 4, dtype=torch.int32, device="cuda") if bytes_alg < 1e9 else None
     ours = lambda: ops.attn_decode(q, kc, vc, lens, bt, SCALE)  # noqa: E731
     med, best = timeit(ours, iters, flush=flush)
-    rec = {"kind": "decode", "B": B, "ctx": ctx, "Hq": Hq, "Hkv": Hkv, "ragged": ragged, "alg_bytes": bytes_alg,
+    # the same launch(es) replayed from a CUDA graph (how the engine runs decode): no host launch cost
+    out_g = torch.empty_like(q)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        ops.attn_decode(q, kc, vc, lens, bt, SCALE, out=out_g)
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        ops.attn_decode(q, kc, vc, lens, bt, SCALE, out=out_g)
+    gmed, gbest = timeit(graph.replay, iters, flush=flush)
+    rec = {"kind": "decode", "graph_ms_median": gmed, "graph_ms_best": gbest, "graph_gbps": bytes_alg / gmed / 1e6,
+           "shape_env": os.environ.get("B200ATTN_DECODE_SHAPE", ""), "B": B, "ctx": ctx, "Hq": Hq, "Hkv": Hkv, "ragged": ragged, "alg_bytes": bytes_alg,
            "ours_ms_median": med, "ours_ms_best": best, "ours_gbps": bytes_alg / med / 1e6,
            "ours_frac_measured_hbm": bytes_alg / med / 1e6 / PEAK["hbm_gbs"], "ours_frac_8TBps": bytes_alg / med / 1e6 / 8000,
            "num_splits": ops.load_library().b200_decode_plan(B, Hkv, nblk_per * PAGE)}
@@ -204,6 +216,11 @@ def main():
         decode_case("cfg2_decode_bs256_ctx384_0p6b", 256, 384, 16, 8, a.iters, results)
         decode_case("decode_bs1_ctx4096_8b", 1, 4096, 32, 8, a.iters, results)
         decode_case("decode_bs8_ctx16384_14b_tp2", 8, 16384, 20, 4, a.iters, results)
+        decode_case("decode_bs256_ctx256_8b", 256, 256, 32, 8, a.iters, results)
+        decode_case("decode_bs256_ctx1280_8b", 256, 1280, 32, 8, a.iters, results)
+        decode_case("decode_bs256_ctx1280_8b_tp4", 256, 1280, 8, 2, a.iters, results)
+        decode_case("decode_bs64_ctx2048_8b", 64, 2048, 32, 8, a.iters, results)
+        decode_case("decode_bs16_ctx1024_8b", 16, 1024, 32, 8, a.iters, results)
     if "prefill" in what:
         prefill_case("prefill_1x8192_causal_hq8", [8192], [8192], 8, 1, max(a.iters // 2, 3), results, variants=(2, 3, 1))
         prefill_case("prefill_4x4096_causal_8b_tp1", [4096] * 4, [4096] * 4, 32, 8, max(a.iters // 2, 3), results)
