@@ -223,6 +223,7 @@ def run_ours(args):
         decode_only()
     ms_decode = timed(decode_only, args.steps) / args.steps
     reset_context()
+    prefill = prefill_leg(ops, device, hq, hkv, scale, timed, world) if not args.no_prefill else None
 
     dec_b, sc_b = algorithmic_bytes(B, CTX, hq, hkv)
     total_bytes = (dec_b + sc_b) * world
@@ -257,6 +258,7 @@ def run_ours(args):
                          "peak_source": peak_src, "algorithmic_bytes_per_launch": dec_b,
                          "ms_per_launch": round(ms_decode, 4), "frac_of_nominal_8TBps": round(achieved / 8000.0, 4)},
             "cpu_baseline": cpu,
+            "prefill": prefill,
             "clocks": clocks,
         }
         sys.stdout.flush()
@@ -264,6 +266,36 @@ def run_ours(args):
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def prefill_leg(ops, device, hq, hkv, scale, timed, world, seqs=4, seqlen=4096, iters=5):
+    """Second half of BASELINE.json's metric ("prefill TFLOP/s"): the persistent tcgen05 prefill kernel on
+    `seqs` x `seqlen` causal self-attention at this rank's head counts (unpaged form, attention.py:242-248).
+    flops = 4*D*Hq*sum_b Lq(Lq+1)/2.  Peak = measured bf16 burst (MEASURED_PEAKS.json)."""
+    T = seqs * seqlen
+    g = torch.Generator(device=device).manual_seed(7)
+    q = torch.randn(T, hq, D, generator=g, device=device, dtype=torch.bfloat16)
+    k = torch.randn(T, hkv, D, generator=g, device=device, dtype=torch.bfloat16)
+    v = torch.randn(T, hkv, D, generator=g, device=device, dtype=torch.bfloat16)
+    cu = torch.arange(0, T + 1, seqlen, dtype=torch.int32, device=device)
+    plan = ops.attn_plan(cu, cu, T, hq, hkv, route_decode=False)
+    out = torch.empty_like(q)
+
+    def run():
+        ops.attn_varlen_planned(q, k, v, cu, cu, seqlen, seqlen, scale, plan=plan, out=out)
+    for _ in range(3):
+        run()
+    ms = timed(run, iters) / iters
+    flops = 4 * D * hq * seqs * (seqlen * (seqlen + 1) // 2)
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peak, src = float(json.load(f)["bf16_tflops"]), "measured (MEASURED_PEAKS.json bf16_tflops, burst)"
+    except Exception:
+        peak, src = 1590.0, "fallback"
+    tf = flops / (ms * 1e-3) / 1e12
+    return {"kernel": "prefill_persist_kernel", "workload": f"{seqs}x{seqlen} causal, {hq}q/{hkv}kv per GPU", "bound": "tensor",
+            "achieved": round(tf * world, 1), "per_gpu": round(tf, 1), "peak": peak, "unit": "TFLOP/s",
+            "frac": round(tf / peak, 4), "peak_source": src, "ms_per_launch": round(ms, 4), "flops_per_launch": flops}
 
 
 def cpu_baseline_sample(num_seqs=32, reps=2):
@@ -330,6 +362,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-prefill", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -444,3 +444,27 @@ def test_fused_norm_rope_store_equals_unfused_then_scatter(ops, Hq, Hkv, T, need
     q2, k2 = ops.qk_norm_rope_store(qd, kd, vd, pos.cuda(), None, None, cache.cuda(), 1e-6, kc, vc, slots.cuda())
     q2r, k2r = ops.qk_norm_rope(qd, kd, pos.cuda(), None, None, cache.cuda())
     assert torch.equal(q2, q2r) and torch.equal(k2, k2r)
+
+
+@pytest.mark.parametrize("Hq,Hkv,splits", [(8, 2, 1), (8, 2, 3), (20, 4, 1), (16, 1, 2)])
+def test_decode_persistent_many_items_dynamic_claims_and_rearm(ops, Hq, Hkv, splits):
+    """More (sequence, kv head, split) items than 3 rounds of the persistent grid (2 CTAs x 148 SMs), so the
+    atomic item counter is exercised; ragged lengths with padding rows scattered through the batch; launched
+    three times back to back on one workspace: every launch must leave the scheduler header zero (re-armed)
+    and produce identical bits."""
+    import random
+    rnd = random.Random(Hq * 31 + splits)
+    B = 1200 // Hkv + 7
+    lens = [rnd.choice([0, 1, 16, 40, 255, 256, 300, 600, 700]) for _ in range(B)]
+    c = make_paged_case(500 + Hq, [1] * B, lens, Hq, Hkv, pad=0, table_width=3)
+    want = oracle.attn_decode(c["q"], c["k_cache"], c["v_cache"], c["context_lens"], c["block_tables"], SCALE)
+    args = (dev(c["q"]), dev(c["k_cache"]), dev(c["v_cache"]), dev(c["context_lens"]), dev(c["block_tables"]), SCALE)
+    outs = [ops.attn_decode(*args, num_splits=splits).clone() for _ in range(3)]
+    torch.cuda.synchronize()
+    ws = ops._WS_CACHE[torch.cuda.current_device()]
+    assert ws[:256].view(torch.int32).abs().sum().item() == 0
+    assert maxerr(outs[0], want) <= ATOL
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[1], outs[2])
+    for b, L in enumerate(lens):
+        if L == 0:
+            assert outs[0][b].abs().sum().item() == 0
