@@ -70,11 +70,8 @@ int b200_kv_scatter(const void* key, const void* value,
  *     block_tables int32[B, >=ceil(len/256)] with row stride bt_row_stride; entries past
  *     the context (-1 eager, 0 graph) are never dereferenced.
  *     num_splits: from b200_decode_plan (host-only heuristic => static under CUDA graphs).
- *     workspace: b200_decode_workspace_bytes(B, Hq, num_splits) bytes (never 0), 16-byte aligned,
- *     REQUIRED for every launch: a 256-byte header holding the persistent kernel's two scheduler
- *     words, followed by the split-K partials.  The caller zero-fills the header ONCE after
- *     allocating; every launch leaves it zero again (the last CTA out re-arms it), so CUDA-graph
- *     replays need no memset.  Launches sharing one workspace must be stream-ordered.
+ *     workspace: b200_decode_workspace_bytes(B, Hq, num_splits) bytes, may be NULL iff
+ *     num_splits == 1.
  */
 int b200_decode_plan(int32_t batch, int32_t num_kv_heads, int32_t max_context_len);
 size_t b200_decode_workspace_bytes(int32_t batch, int32_t num_heads, int32_t num_splits);

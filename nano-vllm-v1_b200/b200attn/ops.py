@@ -52,13 +52,25 @@ def store_kvcache(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor,
 
 
 # ------------------------------------------------------------------------------------ (3)
+class DecodeWorkspace:
+    """Split-K partials, allocated once (allocate_kv_cache time) and reused by every layer."""
+
+    def __init__(self, max_batch: int, num_heads: int, max_splits: int, device) -> None:
+        lib = load_library()
+        self.max_batch, self.num_heads, self.max_splits = max_batch, num_heads, max_splits
+        nbytes = lib.b200_decode_workspace_bytes(max_batch, num_heads, max(max_splits, 2))
+        self.buf = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=device)
+
+    def fits(self, batch: int, num_heads: int, splits: int) -> bool:
+        return load_library().b200_decode_workspace_bytes(batch, num_heads, splits) <= self.buf.numel()
+
+
 _WS_CACHE = {}
 
 
-def _workspace_for(batch: int, num_heads: int, splits: int, device) -> torch.Tensor:
-    """Per-device decode workspace: a 256-byte header (the persistent kernel's two scheduler words, which
-    must be ZERO before the first launch and which every launch leaves zero again) followed by the split-K
-    partials.  Launches sharing it must be stream-ordered (the engine uses one stream)."""
+def _workspace_for(batch: int, num_heads: int, splits: int, device) -> Optional[torch.Tensor]:
+    if splits <= 1:
+        return None
     key = (device.index if device.index is not None else torch.cuda.current_device())
     ws = _WS_CACHE.get(key)
     need = load_library().b200_decode_workspace_bytes(batch, num_heads, splits)
@@ -66,15 +78,16 @@ def _workspace_for(batch: int, num_heads: int, splits: int, device) -> torch.Ten
         if torch.cuda.is_current_stream_capturing():
             raise RuntimeError("b200attn: decode workspace must be sized before CUDA-graph capture "
                                "(call ops.reserve_decode_workspace first)")
-        ws = torch.zeros(int(need * 1.25) + 256, dtype=torch.uint8, device=device)
+        ws = torch.empty(int(need * 1.25) + 256, dtype=torch.uint8, device=device)
         _WS_CACHE[key] = ws
     return ws
 
 
 def reserve_decode_workspace(max_batch: int, num_heads: int, num_kv_heads: int, max_context: int, device) -> None:
-    """Size the per-device decode workspace for the worst graph bucket (call before capture)."""
+    """Size the per-device split-K workspace for the worst graph bucket (call before capture)."""
     lib = load_library()
     worst = 0
+    bs = 1
     cands = sorted({1, 2, 4, 8, *range(16, max_batch + 1, 16), max_batch})
     for bs in cands:
         s = lib.b200_decode_plan(bs, num_kv_heads, max_context)
@@ -82,7 +95,7 @@ def reserve_decode_workspace(max_batch: int, num_heads: int, num_kv_heads: int, 
     key = (torch.device(device).index if torch.device(device).index is not None else torch.cuda.current_device())
     cur = _WS_CACHE.get(key)
     if cur is None or cur.numel() < worst:
-        _WS_CACHE[key] = torch.zeros(worst + 256, dtype=torch.uint8, device=device)
+        _WS_CACHE[key] = torch.empty(worst + 256, dtype=torch.uint8, device=device)
 
 
 def attn_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, context_lens: torch.Tensor,
@@ -107,7 +120,8 @@ def attn_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, c
     check(lib.b200_attn_decode(q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(),
                                out.data_ptr(), out.stride(0), context_lens.data_ptr(),
                                block_tables.data_ptr(), block_tables.stride(0), B, Hq, Hkv, D, PAGE,
-                               float(scale), num_splits, ws.data_ptr(), ws.numel(), _stream()), "b200_attn_decode")
+                               float(scale), num_splits, ws.data_ptr() if ws is not None else None,
+                               ws.numel() if ws is not None else 0, _stream()), "b200_attn_decode")
     return out
 
 
@@ -219,7 +233,8 @@ def attn_varlen_planned(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_se
         ws = _workspace_for(B, Hq, num_splits, q.device)
         check(lib.b200_attn_decode_varlen(q.data_ptr(), q.stride(0), k.data_ptr(), v.data_ptr(), out.data_ptr(), out.stride(0),
                                           cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr(), bt_ptr, bt_stride, B, Hq, Hkv, D,
-                                          PAGE, float(scale), num_splits, ws.data_ptr(), ws.numel(), plan.buf.data_ptr(), plan.buf.numel(),
+                                          PAGE, float(scale), num_splits, ws.data_ptr() if ws is not None else None,
+                                          ws.numel() if ws is not None else 0, plan.buf.data_ptr(), plan.buf.numel(),
                                           _stream()), "b200_attn_decode_varlen")
     return out
 

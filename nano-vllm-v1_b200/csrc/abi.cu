@@ -88,15 +88,8 @@ int b200_decode_plan(int32_t batch, int32_t num_kv_heads, int32_t max_context_le
 }
 
 size_t b200_decode_workspace_bytes(int32_t batch, int32_t num_heads, int32_t num_splits) {
-    if (num_splits <= 1 || batch <= 0 || num_heads <= 0) return DECODE_WS_HEADER_BYTES;
-    return DECODE_WS_HEADER_BYTES + (size_t)batch * num_splits * num_heads * (B200_HD_CONST + 1) * sizeof(float);
-}
-
-static inline void decode_workspace_views(void* workspace, int32_t batch, int32_t num_heads, int32_t num_splits, DecodeArgs& a) {
-    uint8_t* base = (uint8_t*)workspace;
-    a.sched = (uint32_t*)base;
-    a.ws_o = (float*)(base + DECODE_WS_HEADER_BYTES);
-    a.ws_lse = a.ws_o + (size_t)batch * num_splits * num_heads * B200_HD_CONST;
+    if (num_splits <= 1 || batch <= 0 || num_heads <= 0) return 0;
+    return (size_t)batch * num_splits * num_heads * (B200_HD_CONST + 1) * sizeof(float);
 }
 
 int b200_attn_decode(const void* q, int64_t q_token_stride, const void* k_cache, const void* v_cache,
@@ -114,13 +107,14 @@ int b200_attn_decode(const void* q, int64_t q_token_stride, const void* k_cache,
         !stride_ok(q_token_stride) || !stride_ok(out_token_stride))
         return B200_ERR_ALIGN;
     const size_t need = b200_decode_workspace_bytes(batch, num_heads, num_splits);
-    if (!workspace || workspace_bytes < need || !aligned16(workspace)) return B200_ERR_WORKSPACE;
+    if (num_splits > 1 && (!workspace || workspace_bytes < need)) return B200_ERR_WORKSPACE;
     DecodeArgs a;
     a.q = q; a.q_token_stride = q_token_stride; a.k_cache = k_cache; a.v_cache = v_cache;
     a.out = out; a.out_token_stride = out_token_stride; a.context_lens = context_lens;
     a.block_tables = block_tables; a.bt_row_stride = bt_row_stride;
     a.batch = batch; a.Hq = num_heads; a.Hkv = num_kv_heads; a.scale = softmax_scale; a.num_splits = num_splits;
-    decode_workspace_views(workspace, batch, num_heads, num_splits, a);
+    a.ws_o = (float*)workspace;
+    a.ws_lse = workspace ? (float*)workspace + (size_t)batch * num_splits * num_heads * B200_HD_CONST : nullptr;
     return launch_attn_decode(a, (cudaStream_t)stream);
 }
 
@@ -228,14 +222,15 @@ int b200_attn_decode_varlen(const void* q, int64_t q_token_stride, const void* k
         !stride_ok(q_token_stride) || !stride_ok(out_token_stride))
         return B200_ERR_ALIGN;
     const size_t need = b200_decode_workspace_bytes(batch, num_heads, num_splits);
-    if (!workspace || workspace_bytes < need || !aligned16(workspace)) return B200_ERR_WORKSPACE;
+    if (num_splits > 1 && (!workspace || workspace_bytes < need)) return B200_ERR_WORKSPACE;
     if (plan_bytes_given < (size_t)PLAN_HEADER_WORDS * 4 + (size_t)batch * 4) return B200_ERR_WORKSPACE;
     DecodeArgs a;
     a.q = q; a.q_token_stride = q_token_stride; a.k_cache = k_cache; a.v_cache = v_cache;
     a.out = out; a.out_token_stride = out_token_stride; a.context_lens = nullptr;
     a.block_tables = block_tables; a.bt_row_stride = bt_row_stride;
     a.batch = batch; a.Hq = num_heads; a.Hkv = num_kv_heads; a.scale = softmax_scale; a.num_splits = num_splits;
-    decode_workspace_views(workspace, batch, num_heads, num_splits, a);
+    a.ws_o = (float*)workspace;
+    a.ws_lse = workspace ? (float*)workspace + (size_t)batch * num_splits * num_heads * B200_HD_CONST : nullptr;
     const int32_t* pl = (const int32_t*)plan;
     a.cu_q = cu_seqlens_q; a.cu_k = cu_seqlens_k;
     a.n_rows = pl + 1;

@@ -36,13 +36,11 @@ struct DecodeArgs {
     const int32_t* context_lens; const int32_t* block_tables; int32_t bt_row_stride;
     int32_t batch, Hq, Hkv; float scale; int32_t num_splits;
     float* ws_o; float* ws_lse;
-    uint32_t* sched;                 // 2 words of the workspace header, zero between launches (dynamic item claims)
     // varlen form: non-null => rows are row_list[0 .. *n_rows), lengths/tokens from cu_k / cu_q
     const int32_t* cu_q = nullptr; const int32_t* cu_k = nullptr;
     const int32_t* row_list = nullptr; const int32_t* n_rows = nullptr;
 };
 int launch_attn_decode(const DecodeArgs& a, cudaStream_t stream);
-constexpr size_t DECODE_WS_HEADER_BYTES = 256;
 
 struct PrefillArgs {
     const void* q; int64_t q_token_stride;

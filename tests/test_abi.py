@@ -61,8 +61,8 @@ def test_decode_plan_is_static_and_bounded(lib):
     s = lib.b200_decode_plan(64, 1, 32832)                   # cfg5 decode: few items, long context
     assert 2 <= s <= 64
     assert lib.b200_decode_plan(1, 8, 300) <= 2              # never finer than one page per split
-    assert lib.b200_decode_workspace_bytes(4, 32, 1) == 256          # scheduler header only
-    assert lib.b200_decode_workspace_bytes(4, 32, 3) == 256 + 4 * 3 * 32 * 129 * 4
+    assert lib.b200_decode_workspace_bytes(4, 32, 1) == 0
+    assert lib.b200_decode_workspace_bytes(4, 32, 3) == 4 * 3 * 32 * 129 * 4
 
 
 def test_ops_refuse_cpu_tensors(lib):

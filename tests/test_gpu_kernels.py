@@ -447,11 +447,9 @@ def test_fused_norm_rope_store_equals_unfused_then_scatter(ops, Hq, Hkv, T, need
 
 
 @pytest.mark.parametrize("Hq,Hkv,splits", [(8, 2, 1), (8, 2, 3), (20, 4, 1), (16, 1, 2)])
-def test_decode_persistent_many_items_dynamic_claims_and_rearm(ops, Hq, Hkv, splits):
-    """More (sequence, kv head, split) items than 3 rounds of the persistent grid (2 CTAs x 148 SMs), so the
-    atomic item counter is exercised; ragged lengths with padding rows scattered through the batch; launched
-    three times back to back on one workspace: every launch must leave the scheduler header zero (re-armed)
-    and produce identical bits."""
+def test_decode_many_items_ragged_with_padding_rows(ops, Hq, Hkv, splits):
+    """Several waves of (sequence, kv head, split) CTAs; ragged lengths with padding rows scattered through
+    the batch; launched three times back to back on one workspace: identical bits every time."""
     import random
     rnd = random.Random(Hq * 31 + splits)
     B = 1200 // Hkv + 7
@@ -460,9 +458,6 @@ def test_decode_persistent_many_items_dynamic_claims_and_rearm(ops, Hq, Hkv, spl
     want = oracle.attn_decode(c["q"], c["k_cache"], c["v_cache"], c["context_lens"], c["block_tables"], SCALE)
     args = (dev(c["q"]), dev(c["k_cache"]), dev(c["v_cache"]), dev(c["context_lens"]), dev(c["block_tables"]), SCALE)
     outs = [ops.attn_decode(*args, num_splits=splits).clone() for _ in range(3)]
-    torch.cuda.synchronize()
-    ws = ops._WS_CACHE[torch.cuda.current_device()]
-    assert ws[:256].view(torch.int32).abs().sum().item() == 0
     assert maxerr(outs[0], want) <= ATOL
     assert torch.equal(outs[0], outs[1]) and torch.equal(outs[1], outs[2])
     for b, L in enumerate(lens):

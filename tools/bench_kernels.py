@@ -37,7 +37,7 @@ def timeit(fn, iters=20, warm=5, flush=None):
     ts = []
     for _ in range(iters):
         if flush is not None:
-            flush.add_(1)
+            flush.max()                                  # read-only sweep > L2: evicts the working set, leaves no dirty lines
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         fn()
