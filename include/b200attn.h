@@ -48,6 +48,13 @@ const char* b200_status_string(int status);
 /* Number of SMs of the current device (cached); helper for split planning. */
 int b200_sm_count(void);
 
+/* Debug/profiling aid (no reference counterpart): while `dev_buf` (zeroed int64[4][max_tiles][8] in
+ * device memory) is non-NULL, b200_attn_prefill_planned runs an instrumented build whose CTA 0 stamps
+ * clock64 at the phase boundaries of its first `max_tiles` tiles (rows 0/1: softmax warpgroups: wait,
+ * S ready, S loaded, max done, exp done, P published; rows 2/3: MMA issuer: wait P, P seen, issued).
+ * Pass NULL to return to the product kernel.  tools/trace_prefill.py reads it. */
+int b200_debug_prefill_trace(void* dev_buf, int max_tiles);
+
 /* ---------------------------------------------------------------------------------
  * (1) KV-cache scatter.  Replaces store_kvcache_kernel + store_kvcache,
  *     nanovllm/layers/attention.py:34-90 and :93-127.

@@ -12,6 +12,7 @@ SIGNATURES = {
     "b200_version": (c_int32, []),
     "b200_status_string": (c_char_p, [c_int32]),
     "b200_sm_count": (c_int32, []),
+    "b200_debug_prefill_trace": (c_int32, [c_void_p, c_int32]),
     "b200_kv_scatter": (c_int32, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
                                   c_int32, c_int32, c_int32, c_void_p]),
     "b200_decode_plan": (c_int32, [c_int32, c_int32, c_int32]),

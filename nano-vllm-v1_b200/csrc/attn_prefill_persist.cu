@@ -27,7 +27,10 @@ struct PersistParams {
     __nv_bfloat16* out; int64_t out_token_stride;
     int32_t Hq, G, pair_heads; float scale_log2;
     const int32_t* plan; const int32_t* items;
+    long long* trace; int32_t trace_tiles;      // TRACE builds only: clock64 stamps of CTA 0 (b200_debug_prefill_trace)
 };
+
+constexpr int PREFILL_EMU_DEFAULT = 0;
 
 struct PsSmem {
     static constexpr int NQ = 2;
@@ -35,8 +38,8 @@ struct PsSmem {
     static constexpr int K_OFF = Q_OFF + NQ * TC_TILE_BYTES;
     static constexpr int V_OFF = K_OFF + TC_KV_STAGES * TC_TILE_BYTES;
     static constexpr int BAR_OFF = V_OFF + TC_KV_STAGES * TC_TILE_BYTES;
-    // q_full[2] q_empty[2] k_full[S] k_empty[S] v_full[S] v_empty[S] s_full[2] p_full[2] o_final[2]
-    static constexpr int NUM_BARS = 5 * NQ + 4 * TC_KV_STAGES;
+    // q_full[2] q_empty[2] k_full[S] k_empty[S] v_full[S] v_empty[S] s_full[2] p_full[2] o_final[2] p_half[2]
+    static constexpr int NUM_BARS = 6 * NQ + 4 * TC_KV_STAGES;
     static constexpr int TMEM_PTR_OFF = BAR_OFF + NUM_BARS * 8;
     static constexpr int TOTAL = TMEM_PTR_OFF + 16;
     static constexpr int ALLOC = TOTAL + 1024;
@@ -129,6 +132,32 @@ __device__ __forceinline__ uint32_t cvt_bf16x2(float lo, float hi) {
     return r;
 }
 
+// 2^x for two values on the FMA/ALU pipes instead of MUFU.ex2 (which is co-critical with the tensor
+// pipe: 16 ex2/clk/SM).  x = n + r with n = floor(x) taken from the low mantissa bits of
+// (x + 1.5*2^23) rounded towards -inf, 2^r on [0,1) by a degree-3 polynomial (max relative error
+// 8.8e-5, far below the bf16 rounding of P), n added straight into the exponent field.  x is clamped
+// to >= -126 first, so masked (-inf) scores come out as ~2^-126 instead of 0; the epilogue treats a
+// row sum below 1e-30 as "nothing visible" (a row with anything visible has a sum >= 2^-8).
+__device__ __forceinline__ void exp2_poly2(float x0, float x1, float& p0, float& p1) {
+    constexpr float MAGIC = 12582912.f;                             // 2^23 + 2^22
+    const uint64_t x2 = pack2(fmaxf(x0, -126.f), fmaxf(x1, -126.f));
+    uint64_t t2;
+    asm("add.rm.f32x2 %0, %1, %2;" : "=l"(t2) : "l"(x2), "l"(pack2(MAGIC, MAGIC)));
+    const uint64_t n2 = add2(t2, pack2(-MAGIC, -MAGIC));            // floor(x), exact
+    const uint64_t r2 = fma2(n2, pack2(-1.f, -1.f), x2);            // x - floor(x) in [0,1)
+    uint64_t q2 = fma2(r2, pack2(0.077119089663028717041015625f, 0.077119089663028717041015625f),
+                       pack2(0.227564394474029541015625f, 0.227564394474029541015625f));
+    q2 = fma2(q2, r2, pack2(0.695146143436431884765625f, 0.695146143436431884765625f));
+    q2 = fma2(q2, r2, pack2(1.f, 1.f));
+    float q0, q1, t0, t1;
+    unpack2(q2, q0, q1);
+    unpack2(t2, t0, t1);
+    p0 = __uint_as_float(__float_as_uint(q0) + (__float_as_uint(t0) << 23));
+    p1 = __uint_as_float(__float_as_uint(q1) + (__float_as_uint(t1) << 23));
+}
+
+// EMU = how many of every 4 score pairs take the polynomial exp2 instead of MUFU.ex2 (0..4).
+template <int EMU, bool TRACE = false>
 __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
     const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
     const __grid_constant__ CUtensorMap map_v, const PersistParams p) {
@@ -150,6 +179,7 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
     auto s_full = [&](int t) { return bars + 8 * (4 + 4 * S + t); };
     auto p_full = [&](int t) { return bars + 8 * (6 + 4 * S + t); };
     auto o_final = [&](int t) { return bars + 8 * (8 + 4 * S + t); };
+    auto p_half = [&](int t) { return bars + 8 * (10 + 4 * S + t); };
     volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(smem_gen + L::TMEM_PTR_OFF);
     constexpr uint32_t TMEM_COLS = 512;
 
@@ -157,7 +187,7 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
 #pragma unroll
         for (int t = 0; t < 2; ++t) {
             mbar_init(q_full(t), 1); mbar_init(q_empty(t), 1); mbar_init(s_full(t), 1);
-            mbar_init(p_full(t), 128); mbar_init(o_final(t), 1);
+            mbar_init(p_full(t), 128); mbar_init(p_half(t), 128); mbar_init(o_final(t), 1);
         }
 #pragma unroll
         for (int s = 0; s < S; ++s) {
@@ -231,14 +261,17 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
                         tc_mma_ss(d, umma_desc(qst + off, 0, 1024), umma_desc(kst + off, 0, 1024), IDESC_QK, ks > 0);
                     }
                 };
-                auto issue_pv = [&](int t, uint32_t st, bool first) {
+                auto issue_pv = [&](int t, uint32_t st, bool first, int half) {     // K-steps 4*half .. 4*half+3
                     const uint32_t vst = sV + st * TC_TILE_BYTES;
                     const uint32_t d = tmem_base + t * 256 + 128, a = tmem_base + t * 256;
 #pragma unroll
-                    for (int kk = 0; kk < 8; ++kk)
+                    for (int kk = 4 * half; kk < 4 * half + 4; ++kk)
                         tc_mma_ts(d, a + kk * 8, umma_desc(vst + kk * 2048, TC_HALF_BYTES, 1024), IDESC_PV, (!first || kk > 0));
                 };
                 uint32_t kv_it = 0, q_use[2] = {0, 0}, p_cnt[2] = {0, 0};
+                auto stamp = [&](int t, uint32_t n, int e) {
+                    if (TRACE && blockIdx.x == 0 && (int)n < p.trace_tiles) p.trace[((2 + t) * p.trace_tiles + n) * 8 + e] = clock64();
+                };
                 Unit u;
                 for (int k = 0; get_round(p, k, u); ++k) {
 #pragma unroll
@@ -259,16 +292,25 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
                     }
                     for (int j = 0; j < u.n_max; ++j) {
                         const uint32_t it = kv_it + j, st = it % S, par = (it / S) & 1u;
+                        stamp(0, p_cnt[0], 4);
                         mbar_wait(v_full(st), par);
+                        stamp(0, p_cnt[0], 5);
                         if (j + 1 < u.n_max) mbar_wait(k_full((it + 1) % S), ((it + 1) / S) & 1u);
+                        stamp(0, p_cnt[0], 6);
                         tc_fence_after();
 #pragma unroll
                         for (int t = 0; t < 2; ++t) {
                             if (j < u.nt(t)) {
+                                stamp(t, p_cnt[t], 0);
+                                mbar_wait(p_half(t), p_cnt[t] & 1u);
+                                tc_fence_after();
+                                issue_pv(t, st, j == 0, 0);
+                                stamp(t, p_cnt[t], 3);
                                 mbar_wait(p_full(t), p_cnt[t] & 1u);
+                                stamp(t, p_cnt[t], 1);
                                 ++p_cnt[t];
                                 tc_fence_after();
-                                issue_pv(t, st, j == 0);
+                                issue_pv(t, st, false, 1);
                                 if (j + 1 < u.nt(t)) {
                                     issue_qk(t, (it + 1) % S);
                                     tc_commit(s_full(t));
@@ -276,6 +318,7 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
                                 } else {
                                     tc_commit(o_final(t));
                                 }
+                                stamp(t, p_cnt[t] - 1, 2);
                             }
                         }
                         tc_commit(v_empty(st));
@@ -296,6 +339,9 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
         const uint32_t tO = tS + 128;
         const uint64_t scale2 = pack2(p.scale_log2, p.scale_log2);
         uint32_t s_cnt = 0, o_cnt = 0, kv_it = 0;
+        auto stamp = [&](uint32_t n, int e) {
+            if (TRACE && blockIdx.x == 0 && row_in_tile == 0 && (int)n < p.trace_tiles) p.trace[(t * p.trace_tiles + n) * 8 + e] = clock64();
+        };
         Unit u;
         for (int k = 0; get_round(p, k, u); ++k) {
             const int nt = u.nt(t);
@@ -307,26 +353,33 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
 
             for (int j = 0; j < nt; ++j) {
                 const int n0 = j * TC_BN;
+                stamp(s_cnt, 0);
                 mbar_wait(s_full(t), s_cnt & 1u);
+                stamp(s_cnt, 1);
                 ++s_cnt;
                 tc_fence_after();
                 uint32_t s[128];
 #pragma unroll
                 for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&s[c * 32]));
                 tmem_wait_ld();
+                stamp(s_cnt - 1, 2);
                 if ((n0 + TC_BN > u.Lk) || (n0 + TC_BN - 1 > r_begin + offset)) {      // tail or diagonal tile
                     const int lim = min(u.Lk - 1, row + offset) - n0;                  // last visible column of this row
 #pragma unroll
                     for (int i = 0; i < 128; ++i)
                         if (i > lim) s[i] = 0xff800000u;                                // -inf
                 }
-                float mx0 = -INFINITY, mx1 = -INFINITY;
+                // 8 independent max chains (FMNMX3 latency would serialise 2 chains of 32)
+                float mxc[8];
 #pragma unroll
-                for (int i = 0; i < 128; i += 4) {
-                    mx0 = max3(mx0, __uint_as_float(s[i]), __uint_as_float(s[i + 1]));
-                    mx1 = max3(mx1, __uint_as_float(s[i + 2]), __uint_as_float(s[i + 3]));
-                }
-                const float mx = fmaxf(mx0, mx1) * p.scale_log2;
+                for (int c = 0; c < 8; ++c) mxc[c] = -INFINITY;
+#pragma unroll
+                for (int i = 0; i < 128; i += 16)
+#pragma unroll
+                    for (int c = 0; c < 8; ++c)
+                        mxc[c] = max3(mxc[c], __uint_as_float(s[i + 2 * c]), __uint_as_float(s[i + 2 * c + 1]));
+                const float mx0 = max3(mxc[0], mxc[1], mxc[2]), mx1 = max3(mxc[3], mxc[4], mxc[5]);
+                const float mx = max3(mx0, mx1, fmaxf(mxc[6], mxc[7])) * p.scale_log2;
                 // lazy rescale: keep exponentiating against m_used until some row's max outgrows it by 2^8
                 const bool grow = mx > m_used + TC_RESCALE_THRESHOLD || (m_used == -INFINITY && mx > -INFINITY);
                 if (__any_sync(0xffffffffu, grow)) {
@@ -351,22 +404,9 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
                         }
                     }
                 }
+                stamp(s_cnt - 1, 3);
                 const float neg_m = m_used == -INFINITY ? 0.f : -m_used;
                 const uint64_t negm2 = pack2(neg_m, neg_m);
-#pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    uint32_t pk[16];
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        float x0, x1;
-                        unpack2(fma2(pack2(__uint_as_float(s[c * 32 + 2 * i]), __uint_as_float(s[c * 32 + 2 * i + 1])), scale2, negm2), x0, x1);
-                        const float p0 = fast_exp2(x0), p1 = fast_exp2(x1);
-                        l2 = add2(l2, pack2(p0, p1));
-                        pk[i] = cvt_bf16x2(p0, p1);
-                    }
-                    tmem_st16(tS + c * 16, pk);                     // P over the first 64 columns of S
-                }
-                tmem_wait_st();
                 if (n0 + TC_BN > u.Lk) {
                     // Rows of the V tile past the context may hold NaN garbage (torch.empty cache):
                     // 0 * NaN would poison O, so zero them in shared memory before PV reads them.
@@ -380,8 +420,45 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
                     }
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 }
+                // Software-pipelined exponentials: the consumer (row sum, bf16 pack, TMEM store) of pair k
+                // runs EXP_LAG pairs behind its MUFU.ex2 issue, so the in-order warp never stalls on MUFU
+                // latency; two row-sum accumulators break the FADD2 chain.  The first 64 columns of P (KV
+                // rows 0..63 = the first four K-steps of PV) are published early through p_half so the
+                // tensor pipe starts PV while the second half is still being exponentiated.
+                {
+                    constexpr int EXP_LAG = 6, HALF_AT = 32 + EXP_LAG + 6;
+                    uint64_t acc1 = pack2(0.f, 0.f);
+                    uint32_t pk[16];
+#pragma unroll
+                    for (int i = 0; i < 64 + EXP_LAG; ++i) {
+                        if (i < 64) {
+                            float x0, x1, p0, p1;
+                            unpack2(fma2(pack2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), scale2, negm2), x0, x1);
+                            if ((i & 3) < EMU) exp2_poly2(x0, x1, p0, p1);
+                            else { p0 = fast_exp2(x0); p1 = fast_exp2(x1); }
+                            s[2 * i] = __float_as_uint(p0); s[2 * i + 1] = __float_as_uint(p1);
+                        }
+                        if (i >= EXP_LAG) {
+                            const int k = i - EXP_LAG;
+                            const float p0 = __uint_as_float(s[2 * k]), p1 = __uint_as_float(s[2 * k + 1]);
+                            if (k & 1) acc1 = add2(acc1, pack2(p0, p1));
+                            else l2 = add2(l2, pack2(p0, p1));
+                            pk[k & 15] = cvt_bf16x2(p0, p1);
+                            if ((k & 15) == 15) tmem_st16(tS + (k >> 4) * 16, pk);
+                        }
+                        if (i == HALF_AT) {                         // stores of columns 0..63 were issued 6 pairs ago
+                            tmem_wait_st();
+                            tc_fence_before();
+                            mbar_arrive(p_half(t));
+                        }
+                    }
+                    l2 = add2(l2, acc1);
+                }
+                stamp(s_cnt - 1, 4);
+                tmem_wait_st();
                 tc_fence_before();
                 mbar_arrive(p_full(t));
+                stamp(s_cnt - 1, 5);
             }
             kv_it += u.n_max;
 
@@ -393,7 +470,7 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
                 float la, lb;
                 unpack2(l2, la, lb);
                 const float l_sum = la + lb;
-                const float inv = l_sum > 0.f ? 1.f / l_sum : 0.f;
+                const float inv = l_sum > 1e-30f ? 1.f / l_sum : 0.f;  // see exp2_poly2 on masked scores
                 __nv_bfloat16* orow = p.out + (int64_t)(u.q0 + row) * p.out_token_stride + (int64_t)u.head(t) * B200_HD;
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
@@ -428,14 +505,24 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
     }
 }
 
+static long long* g_trace = nullptr;
+static int g_trace_tiles = 0;
+
 int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32_t max_items, cudaStream_t stream) {
     if (a.batch == 0 || a.total_q == 0 || a.max_q == 0) return 0;
     if (get_encode_fn() == nullptr) return -6;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(prefill_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PsSmem::ALLOC);
-        if (e != cudaSuccess) return (int)e;
-        attr_set = true;
+    using KernelFn = void (*)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const PersistParams);
+    static const KernelFn kernels[5] = {prefill_persist_kernel<0>, prefill_persist_kernel<1>, prefill_persist_kernel<2>,
+                                        prefill_persist_kernel<3>, prefill_persist_kernel<4>};
+    static int emu = -1;
+    if (emu < 0) {
+        for (int i = 0; i < 5; ++i) {
+            cudaError_t e = cudaFuncSetAttribute(kernels[i], cudaFuncAttributeMaxDynamicSharedMemorySize, PsSmem::ALLOC);
+            if (e != cudaSuccess) return (int)e;
+        }
+        const char* env = getenv("B200ATTN_PREFILL_EMU");        // A/B knob; default chosen by measurement
+        int v = env ? atoi(env) : PREFILL_EMU_DEFAULT;
+        emu = v < 0 ? 0 : (v > 4 ? 4 : v);
     }
     CUtensorMap mq, mk, mv;
     const bool paged = a.block_tables != nullptr;
@@ -458,8 +545,27 @@ int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32
     int grid = sm_count();
     if (units < grid) grid = (int)units;
     if (grid < 1) grid = 1;
-    prefill_persist_kernel<<<grid, 384, PsSmem::ALLOC, stream>>>(mq, mk, mv, p);
+    p.trace = g_trace; p.trace_tiles = g_trace_tiles;
+    if (g_trace != nullptr) {
+        static bool trace_attr = false;
+        if (!trace_attr) {
+            cudaFuncSetAttribute(prefill_persist_kernel<PREFILL_EMU_DEFAULT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, PsSmem::ALLOC);
+            trace_attr = true;
+        }
+        prefill_persist_kernel<PREFILL_EMU_DEFAULT, true><<<grid, 384, PsSmem::ALLOC, stream>>>(mq, mk, mv, p);
+    } else {
+        kernels[emu]<<<grid, 384, PsSmem::ALLOC, stream>>>(mq, mk, mv, p);
+    }
     return (int)cudaGetLastError();
 }
 
 }  // namespace b200
+
+// Debug only: when `dev_buf` (int64[4][max_tiles][8], zeroed by the caller) is non-null, the next
+// persistent prefill launches run the TRACE build and CTA 0 stamps clock64 at the phase boundaries of
+// its first `max_tiles` tiles (rows 0/1: softmax warpgroups, rows 2/3: the MMA issuer's view of them).
+extern "C" int b200_debug_prefill_trace(void* dev_buf, int max_tiles) {
+    b200::g_trace = (long long*)dev_buf;
+    b200::g_trace_tiles = dev_buf ? max_tiles : 0;
+    return 0;
+}

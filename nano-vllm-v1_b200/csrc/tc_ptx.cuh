@@ -26,6 +26,11 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+// try_wait suspends the warp in hardware until the phase completes or this many ns pass, so a waiting
+// role does not steal issue slots from the softmax warp sharing its SM sub-partition.
+#ifndef TC_WAIT_HINT_NS
+#define TC_WAIT_HINT_NS 20000u
+#endif
 // Bounded wait: a protocol bug traps (launch failure) after ~2 s instead of hanging the GPU.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     uint32_t done = 0;
@@ -33,9 +38,9 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     for (uint32_t spin = 0;; ++spin) {
         asm volatile(
             "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
             "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+            : "=r"(done) : "r"(bar), "r"(parity), "r"(TC_WAIT_HINT_NS) : "memory");
         if (done) return;
         if ((spin & 255u) == 255u) {
             uint64_t now;

@@ -91,6 +91,9 @@ def decode_case(name, B, ctx, Hq, Hkv, iters, results, ragged=False):
     del kc, vc
 
 
+PS_ONLY = False    # --ps-only: time just the persistent prefill kernel (A/B sweeps over env knobs)
+
+
 def pairs(lq, lk):
     return lq * (lk - lq) + lq * (lq + 1) // 2
 
@@ -121,7 +124,7 @@ def prefill_case(name, lens_q, lens_k, Hq, Hkv, iters, results, variants=(2, 1),
     flops = 4 * D * Hq * sum(pairs(a, b) for a, b in zip(lens_q, lens_k))
     rec = {"kind": "prefill", "B": B, "T": T, "max_q": max(lens_q), "max_k": max(lens_k), "Hq": Hq, "Hkv": Hkv, "flops": flops}
     outs = {}
-    for v in variants:
+    for v in (() if PS_ONLY else variants):
         fn = lambda: ops.attn_varlen(q, kc, vc, cu_q, cu_k, max(lens_q), max(lens_k), SCALE, block_table=bt, variant=v)  # noqa: E731
         med, best = timeit(fn, iters, warm=2)
         tag = {1: "mma", 2: "tc2", 3: "tc1"}[v]
@@ -139,7 +142,7 @@ def prefill_case(name, lens_q, lens_k, Hq, Hkv, iters, results, variants=(2, 1),
                 "ps_frac_bf16_burst": flops / med / 1e9 / PEAK["bf16_tflops"],
                 "ps_frac_bf16_sustained": flops / med / 1e9 / PEAK["bf16_tflops_sustained"]})
     outs["ps"] = fn()
-    if flash_attn is not None:
+    if flash_attn is not None and not PS_ONLY:
         fa = lambda: flash_attn.flash_attn_varlen_func(q, kc, vc, cu_seqlens_q=cu_q, cu_seqlens_k=cu_k, max_seqlen_q=max(lens_q),  # noqa: E731
                                                        max_seqlen_k=max(lens_k), softmax_scale=SCALE, causal=True, block_table=bt)
         fmed, fbest = timeit(fa, iters, warm=2)
@@ -205,7 +208,10 @@ def main():
     ap.add_argument("--what", default="decode,prefill,pointwise")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "kernels.json"))
     ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--ps-only", action="store_true")
     a = ap.parse_args()
+    global PS_ONLY
+    PS_ONLY = a.ps_only
     results = {"peaks": PEAK, "gpu": torch.cuda.get_device_name(0)}
     what = a.what.split(",")
     if "decode" in what:
