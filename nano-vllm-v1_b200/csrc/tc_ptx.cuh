@@ -114,6 +114,11 @@ __host__ __device__ constexpr uint32_t umma_idesc(uint32_t b_mn_major) {
     return (1u << 4) | (1u << 7) | (1u << 10) | (0u << 15) | (b_mn_major << 16) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
 }
 
+// Same with an explicit N (multiple of 8 at cta_group::1), M=128.
+__host__ __device__ constexpr uint32_t umma_idesc_n(uint32_t b_mn_major, uint32_t n) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | (0u << 15) | (b_mn_major << 16) | ((n >> 3) << 17) | ((128u >> 4) << 24);
+}
+
 // ---------------------------------------------------------------------------------------------
 // host side: tensor maps + launch
 // ---------------------------------------------------------------------------------------------
