@@ -277,6 +277,84 @@ def test_planned_chunked_prefix_rows(ops):
     assert maxerr(got, want) <= ATOL
 
 
+def test_prefill_full_size_cfg5_properties(ops):
+    """BASELINE configs[4] at full per-rank size (TP8: 8q/1kv; one 32,832-token row + 63 rows of 64
+    new tokens over the same 32,768-token cached prefix).  Too big for the CPU oracle, so:
+    (a) sampled query rows against the oracle restricted to those rows, (b) V == const => output ==
+    const, (c) linearity in V, (d) branches given identical queries and tails give identical outputs."""
+    Hq, Hkv, D, P = 8, 1, 128, 256
+    prefix, tail, nbr = 32768, 64, 63
+    lens_q = [prefix + tail] + [tail] * nbr
+    lens_k = [prefix + tail] * (nbr + 1)
+    shared = prefix // P
+    nblk = shared + (nbr + 1) + 1
+    g = torch.Generator(device="cuda").manual_seed(5)
+    kc = torch.randn(nblk, P, Hkv, D, generator=g, device="cuda", dtype=torch.bfloat16)
+    vc = torch.randn(nblk, P, Hkv, D, generator=g, device="cuda", dtype=torch.bfloat16)
+    bt = torch.empty(nbr + 1, shared + 1, dtype=torch.int32)
+    bt[:, :shared] = torch.arange(shared, dtype=torch.int32)
+    bt[:, shared] = torch.arange(shared, shared + nbr + 1, dtype=torch.int32)
+    # branches 1 and 2 get the same tail K/V and the same queries (property d)
+    kc[shared + 2].copy_(kc[shared + 1]); vc[shared + 2].copy_(vc[shared + 1])
+    T = sum(lens_q)
+    q = torch.randn(T, Hq, D, generator=g, device="cuda", dtype=torch.bfloat16)
+    cu_q = torch.tensor([0] + list(torch.tensor(lens_q).cumsum(0)), dtype=torch.int32)
+    cu_k = torch.tensor([0] + list(torch.tensor(lens_k).cumsum(0)), dtype=torch.int32)
+    q[cu_q[2]:cu_q[3]].copy_(q[cu_q[1]:cu_q[2]])
+    run = lambda v: ops.attn_varlen_planned(q, kc, v, cu_q.cuda(), cu_k.cuda(), max(lens_q), max(lens_k), SCALE,  # noqa: E731
+                                            block_table=bt.cuda())
+    out = run(vc)
+    assert torch.isfinite(out.float()).all()
+    # (d)
+    assert torch.equal(out[cu_q[1]:cu_q[2]], out[cu_q[2]:cu_q[3]])
+    # (a) rows of the long sequence and of one branch, exact attention in fp32 on the CPU
+    kflat = kc[bt[0].long().cuda()].reshape(-1, D).float().cpu()
+    vflat = vc[bt[0].long().cuda()].reshape(-1, D).float().cpu()
+    for r in (0, 127, 128, 4095, 20000, prefix + tail - 1):
+        qr = q[r].float().cpu()                                       # [Hq, D]
+        sc = (qr @ kflat[: r + 1].T) * SCALE
+        want = torch.softmax(sc, dim=-1) @ vflat[: r + 1]
+        assert maxerr(out[r], want) <= ATOL
+    k5 = kc[bt[5].long().cuda()].reshape(-1, D).float().cpu()
+    v5 = vc[bt[5].long().cuda()].reshape(-1, D).float().cpu()
+    for i in (0, 63):
+        qr = q[cu_q[5] + i].float().cpu()
+        vis = prefix + i + 1
+        want = torch.softmax((qr @ k5[:vis].T) * SCALE, dim=-1) @ v5[:vis]
+        assert maxerr(out[cu_q[5] + i], want) <= ATOL
+    # (c) out(V1 + V2) == out(V1) + out(V2) up to bf16 rounding of inputs/outputs
+    v2 = torch.randn(vc.shape, generator=g, device="cuda", dtype=torch.bfloat16)
+    vs = (vc.float() + v2.float()).bfloat16()
+    lin = run(vs).float() - (out.float() + run(v2).float())
+    assert lin.abs().max().item() <= 3e-2
+    # (b)
+    const = torch.randn(Hkv, D, generator=torch.Generator().manual_seed(6)).bfloat16().cuda()
+    vconst = const.view(1, 1, Hkv, D).expand_as(vc).contiguous()
+    outc = run(vconst)
+    expect = const.repeat_interleave(Hq // Hkv, dim=0).unsqueeze(0).expand(T, Hq, D)
+    assert maxerr(outc, expect) <= 2 ** -7 * const.abs().max().item() + 1e-6
+
+
+def test_prefill_full_size_warmup_call_properties(ops):
+    """The largest attention call of a run: the reference's warm-up (model_runner.py:311-316), one
+    unpaged 40,960-token causal row (here at the TP8 head count 4q/1kv to bound time).  Sampled
+    rows against exact fp32 attention; V == const => output == const."""
+    T, Hq, Hkv, D = 40960, 4, 1, 128
+    g = torch.Generator(device="cuda").manual_seed(7)
+    q = torch.randn(T, Hq, D, generator=g, device="cuda", dtype=torch.bfloat16)
+    k = torch.randn(T, Hkv, D, generator=g, device="cuda", dtype=torch.bfloat16)
+    v = torch.randn(T, Hkv, D, generator=g, device="cuda", dtype=torch.bfloat16)
+    cu = torch.tensor([0, T], dtype=torch.int32, device="cuda")
+    out = ops.attn_varlen_planned(q, k, v, cu, cu, T, T, SCALE)
+    kf, vf = k[:, 0].float().cpu(), v[:, 0].float().cpu()
+    for r in (0, 1, 129, 8191, 40959):
+        want = torch.softmax((q[r].float().cpu() @ kf[: r + 1].T) * SCALE, dim=-1) @ vf[: r + 1]
+        assert maxerr(out[r], want) <= ATOL
+    const = torch.randn(Hkv, D, generator=torch.Generator().manual_seed(8)).bfloat16().cuda()
+    outc = ops.attn_varlen_planned(q, k, const.view(1, Hkv, D).expand(T, Hkv, D).contiguous(), cu, cu, T, T, SCALE)
+    assert maxerr(outc, const.expand(T, Hq, D)) <= 2 ** -7 * const.abs().max().item() + 1e-6
+
+
 # ---------------------------------------------------------------------------- Attention.forward
 def test_attention_forward_prefix_sharing_same_step(ops):
     """a branch scheduled in the same step reads prefix blocks that another sequence
