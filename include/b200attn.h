@@ -48,6 +48,22 @@ const char* b200_status_string(int status);
 /* Number of SMs of the current device (cached); helper for split planning. */
 int b200_sm_count(void);
 
+/* ---- (f3) small-message tensor-parallel all-reduce over NVLink peer memory ----------------------
+ * Replaces dist.all_reduce(y) in RowParallelLinear.forward (nanovllm/layers/linear.py:407-410) for
+ * bf16 messages up to the `max_msg_bytes` the communicator was created with; larger messages stay on
+ * the reference's NCCL call.  One process per GPU: every rank b200_ar_alloc()s one buffer, the 64-byte
+ * IPC handles are exchanged by the host (the drop-in uses torch.distributed.all_gather_object on the
+ * reference's own process group), peers are mapped with b200_ar_open(), and b200_ar_create() builds the
+ * communicator (peer_ptrs[rank] = the local buffer).  b200_allreduce_bf16 sums `data` (n_elems bf16,
+ * multiple of 8, 16-byte aligned) over all ranks IN PLACE, one kernel launch, stream-ordered, CUDA-graph
+ * capturable; all ranks must call it in the same order with the same n_elems.  two_shot != 0 selects the
+ * reduce-scatter + all-gather form (world > 2), 0 the one-shot form.  Results are bit-identical on all ranks. */
+size_t b200_ar_buffer_bytes(size_t max_msg_bytes);
+int b200_ar_alloc(size_t bytes, void** dev_ptr, void* ipc_handle_out64);
+int b200_ar_open(const void* ipc_handle64, void** peer_ptr);
+int b200_ar_create(int rank, int world, void* const* peer_ptrs, size_t max_msg_bytes, void** comm_out);
+int b200_allreduce_bf16(void* comm, void* data, int64_t n_elems, int two_shot, void* stream);
+
 /* Debug/profiling aid (no reference counterpart): while `dev_buf` (zeroed int64[4][max_tiles][8] in
  * device memory) is non-NULL, b200_attn_prefill_planned runs an instrumented build whose CTA 0 stamps
  * clock64 at the phase boundaries of its first `max_tiles` tiles (rows 0/1: softmax warpgroups: wait,

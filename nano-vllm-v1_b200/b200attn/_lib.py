@@ -1,7 +1,7 @@
 """ctypes binding of include/b200attn.h.  Fails loudly when the library is absent."""
 import ctypes
 import os
-from ctypes import c_char_p, c_float, c_int32, c_int64, c_size_t, c_void_p
+from ctypes import POINTER, c_char_p, c_float, c_int32, c_int64, c_size_t, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
@@ -13,6 +13,11 @@ SIGNATURES = {
     "b200_status_string": (c_char_p, [c_int32]),
     "b200_sm_count": (c_int32, []),
     "b200_debug_prefill_trace": (c_int32, [c_void_p, c_int32]),
+    "b200_ar_buffer_bytes": (c_size_t, [c_size_t]),
+    "b200_ar_alloc": (c_int32, [c_size_t, POINTER(c_void_p), c_void_p]),
+    "b200_ar_open": (c_int32, [c_void_p, POINTER(c_void_p)]),
+    "b200_ar_create": (c_int32, [c_int32, c_int32, POINTER(c_void_p), c_size_t, POINTER(c_void_p)]),
+    "b200_allreduce_bf16": (c_int32, [c_void_p, c_void_p, c_int64, c_int32, c_void_p]),
     "b200_kv_scatter": (c_int32, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
                                   c_int32, c_int32, c_int32, c_void_p]),
     "b200_decode_plan": (c_int32, [c_int32, c_int32, c_int32]),

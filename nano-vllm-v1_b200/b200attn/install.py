@@ -87,6 +87,9 @@ def install(pointwise: bool = True, runner: bool = True) -> None:
         importlib.import_module("nanovllm.layers.layernorm").RMSNorm.forward = _rmsnorm_forward
         importlib.import_module("nanovllm.layers.rotary_embedding").RotaryEmbedding.forward = _rotary_forward
         importlib.import_module("nanovllm.layers.activation").SiluAndMul.forward = _silu_forward
+    if os.environ.get("B200ATTN_ALLREDUCE", "0") == "1":      # opt-in: measured neutral end to end
+        from .layers.linear import row_parallel_forward
+        importlib.import_module("nanovllm.layers.linear").RowParallelLinear.forward = row_parallel_forward
     if runner:
         from .engine import model_runner as ours
         mr = importlib.import_module("nanovllm.engine.model_runner")

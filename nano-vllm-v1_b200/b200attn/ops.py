@@ -314,3 +314,77 @@ def silu_and_mul(x: torch.Tensor) -> torch.Tensor:
     out = torch.empty(x.shape[:-1] + (inter,), dtype=x.dtype, device=x.device)
     check(load_library().b200_silu_and_mul(x.data_ptr(), out.data_ptr(), T, inter, _stream()), "b200_silu_and_mul")
     return out
+
+
+# ---------------------------------------------------------------------------- (f3) TP all-reduce
+class TpAllReduce:
+    """Small-message all-reduce over NVLink peer memory (csrc/allreduce.cu) for the partial sums of
+    RowParallelLinear (nanovllm/layers/linear.py:407-410).  One instance per process; the IPC handles
+    travel through the reference's own torch.distributed group.  Messages larger than `max_bytes`
+    (prefill-sized) stay on dist.all_reduce, exactly the reference's call."""
+
+    def __init__(self, rank: int, world: int, max_bytes: int, gather_handles):
+        import ctypes
+        lib = load_library()
+        self.rank, self.world, self.max_bytes = rank, world, max_bytes
+        self.two_shot_min_bytes = int(__import__("os").environ.get("B200ATTN_AR_TWO_SHOT_MIN", 256 * 1024))
+        nbytes = lib.b200_ar_buffer_bytes(max_bytes)
+        ptr, handle = ctypes.c_void_p(), ctypes.create_string_buffer(64)
+        check(lib.b200_ar_alloc(nbytes, ctypes.byref(ptr), handle), "b200_ar_alloc")
+        handles = gather_handles(bytes(handle.raw))             # list of `world` 64-byte handles, rank order
+        assert len(handles) == world and handles[rank] == bytes(handle.raw)
+        peers = (ctypes.c_void_p * world)()
+        for r in range(world):
+            if r == rank:
+                peers[r] = ptr.value
+            else:
+                p = ctypes.c_void_p()
+                check(lib.b200_ar_open(ctypes.create_string_buffer(handles[r], 64), ctypes.byref(p)), "b200_ar_open")
+                peers[r] = p.value
+        comm = ctypes.c_void_p()
+        check(lib.b200_ar_create(rank, world, peers, max_bytes, ctypes.byref(comm)), "b200_ar_create")
+        self._comm, self._lib = comm, lib
+
+    def fits(self, t: torch.Tensor) -> bool:
+        return (t.is_cuda and t.dtype == torch.bfloat16 and t.is_contiguous() and t.numel() % 8 == 0
+                and t.numel() * 2 <= self.max_bytes and t.data_ptr() % 16 == 0)
+
+    def all_reduce_(self, t: torch.Tensor, two_shot: Optional[bool] = None) -> torch.Tensor:
+        if not self.fits(t):
+            raise RuntimeError("b200attn: tensor does not fit the peer-memory all-reduce (bf16, contiguous, "
+                               f"numel % 8 == 0, <= {self.max_bytes} bytes)")
+        if two_shot is None:
+            two_shot = self.world > 2 and t.numel() * 2 >= self.two_shot_min_bytes
+        check(self._lib.b200_allreduce_bf16(self._comm, t.data_ptr(), t.numel(), 1 if two_shot else 0, _stream()),
+              "b200_allreduce_bf16")
+        return t
+
+
+_TP_AR = None
+# Measured on B200 NVSwitch boxes (tools/ar_check.py, profiles/r1h_allreduce_tp{2,4}.json): the one-shot
+# kernel is ~2x faster than NCCL 2.28 up to 8-32 KB (9-10 us vs 13-19 us per graph-replayed call) and ties or
+# loses above (NCCL reduces in the switch), so only messages up to this size leave NCCL by default.
+AR_DEFAULT_MAX_BYTES = 32 << 10
+
+
+def tp_all_reduce_(t: torch.Tensor) -> torch.Tensor:
+    """In-place sum over the tensor-parallel group: peer-memory kernel when the message fits, the
+    reference's dist.all_reduce otherwise.  The communicator is built on first use, which every rank
+    reaches at the same point (the first forward of the warm-up, model_runner.py:311-316)."""
+    import os
+    import torch.distributed as dist
+    global _TP_AR
+    if _TP_AR is None:
+        world = dist.get_world_size()
+        if world > 8:
+            _TP_AR = False
+        else:
+            def gather(mine: bytes):
+                out = [None] * world
+                dist.all_gather_object(out, mine)
+                return out
+            _TP_AR = TpAllReduce(dist.get_rank(), world, int(os.environ.get("B200ATTN_AR_MAX_BYTES", AR_DEFAULT_MAX_BYTES)), gather)
+    if _TP_AR is not False and _TP_AR.fits(t):
+        return _TP_AR.all_reduce_(t)
+    dist.all_reduce(t)
+    return t

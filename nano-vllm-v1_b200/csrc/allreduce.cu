@@ -1,0 +1,222 @@
+// (f3) Small-message tensor-parallel all-reduce over NVLink peer memory.
+//
+// Replaces dist.all_reduce(y) after o_proj / down_proj (linear.py:407-410) for decode-sized messages:
+// the bf16 partial sums of N ranks ([tokens, hidden], <= B200_AR_MAX_BYTES) are summed in ONE kernel
+// launch per rank, no NCCL call, CUDA-graph capturable.  Every rank owns one cudaMalloc'ed buffer that
+// its peers map through CUDA IPC (NVSwitch gives every pair full bandwidth, so all traffic is direct
+// peer loads):
+//
+//   [ slot 0 | slot 1 | arrival flags A[world][blocks] | arrival flags B[world][blocks] ]
+//
+// One-shot (world == 2 or small messages): block b copies its share of the input into the local slot,
+// publishes "epoch" into flag A[me][b] of every peer (st.release.sys after a system fence), waits until
+// all peers' flags for block b arrived (ld.acquire.sys), then sums that share over all ranks' slots in
+// rank order in fp32 and writes bf16 back in place.  Two-shot (larger messages, world > 2): after the
+// same first barrier a rank reduces only ITS 1/world of the message, writes the result into its own
+// slot, a second barrier (flags B) publishes it, and every rank gathers the reduced parts.  Either way
+// all ranks add in the same order, so they hold bit-identical results (required: every rank samples
+// nothing, but all must feed identical activations to the next layer).
+// Slots alternate with the epoch, so a rank that runs ahead into the next all-reduce never overwrites
+// data a slower peer is still reading: it cannot pass that call's barrier before the peer got there.
+// The epoch lives in device memory and is advanced by the kernel itself (last block out), so a captured
+// graph replays correctly.  Waits are bounded: a protocol bug traps instead of hanging the GPU.
+#include <cstring>
+
+#include "../../include/b200attn.h"
+#include "launch.h"
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int AR_MAX_WORLD = 8;
+constexpr int AR_BLOCKS = 48;                   // blocks per launch == barrier lanes per rank
+constexpr int AR_THREADS = 512;
+
+struct ArComm {
+    uint8_t* peer[AR_MAX_WORLD];                // IPC-mapped buffers, peer[rank] is the local one
+    int32_t rank, world;
+    size_t slot_bytes;
+    uint32_t* epoch;                            // device: [0] = completed all-reduces, [1] = blocks done in this launch
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// All ranks' block b meet here.  `flags_off` selects flag set A or B inside each rank's buffer.
+__device__ __forceinline__ void ar_barrier(const ArComm& c, size_t flags_off, uint32_t epoch) {
+    __syncthreads();                            // this block's stores are ordered before the fence below
+    if ((int)threadIdx.x < c.world) {
+        __threadfence_system();
+        uint32_t* theirs = reinterpret_cast<uint32_t*>(c.peer[threadIdx.x] + flags_off) + c.rank * AR_BLOCKS + blockIdx.x;
+        st_release_sys(theirs, epoch);
+        const uint32_t* mine = reinterpret_cast<const uint32_t*>(c.peer[c.rank] + flags_off) + threadIdx.x * AR_BLOCKS + blockIdx.x;
+        uint32_t spins = 0;
+        while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0)
+            if (++spins > (1u << 27)) __trap();
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ uint4 ld_cg_u4(const void* p) { return __ldcg(reinterpret_cast<const uint4*>(p)); }
+
+__device__ __forceinline__ void acc_bf16x8(float (&a)[8], const uint4& v) {
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float2 f = unpack_bf16x2(w[i]);
+        a[2 * i] += f.x; a[2 * i + 1] += f.y;
+    }
+}
+__device__ __forceinline__ uint4 pack_bf16x8(const float (&a)[8]) {
+    return make_uint4(pack_bf16x2(a[0], a[1]), pack_bf16x2(a[2], a[3]), pack_bf16x2(a[4], a[5]), pack_bf16x2(a[6], a[7]));
+}
+
+// n16 = message size in 16-byte chunks (8 bf16).  In place on `data`.
+template <bool TWO_SHOT>
+__global__ void __launch_bounds__(AR_THREADS) allreduce_kernel(const ArComm c, uint4* data, int64_t n16) {
+    const uint32_t epoch = c.epoch[0] + 1;
+    const size_t slot_off = (epoch & 1u) * c.slot_bytes;
+    const size_t flags_a = 2 * c.slot_bytes, flags_b = flags_a + sizeof(uint32_t) * AR_MAX_WORLD * AR_BLOCKS;
+    uint4* my_slot = reinterpret_cast<uint4*>(c.peer[c.rank] + slot_off);
+    const int64_t stride = (int64_t)gridDim.x * AR_THREADS;
+    const int64_t tid = (int64_t)blockIdx.x * AR_THREADS + threadIdx.x;
+
+    if (!TWO_SHOT) {
+        // block b owns chunks {tid + k*stride}: the same set on every rank, so a per-block barrier suffices
+        for (int64_t i = tid; i < n16; i += stride) my_slot[i] = data[i];
+        ar_barrier(c, flags_a, epoch);
+        int64_t i = tid;
+        for (; i + 3 * stride < n16; i += 4 * stride) {         // 4 x world independent 16-byte peer loads in flight
+            uint4 v[4][AR_MAX_WORLD];
+#pragma unroll
+            for (int r = 0; r < AR_MAX_WORLD; ++r)
+                if (r < c.world) {
+                    const uint4* src = reinterpret_cast<const uint4*>(c.peer[r] + slot_off) + i;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) v[k][r] = ld_cg_u4(src + k * stride);
+                }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int r = 0; r < AR_MAX_WORLD; ++r)
+                    if (r < c.world) acc_bf16x8(a, v[k][r]);
+                data[i + k * stride] = pack_bf16x8(a);
+            }
+        }
+        for (; i < n16; i += stride) {
+            float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            for (int r = 0; r < c.world; ++r) acc_bf16x8(a, ld_cg_u4(reinterpret_cast<const uint4*>(c.peer[r] + slot_off) + i));
+            data[i] = pack_bf16x8(a);
+        }
+    } else {
+        // part p of the message = chunks [p*per, min((p+1)*per, n16)); block b owns {tid + k*stride} inside every part
+        const int64_t per = (n16 + c.world - 1) / c.world;
+        for (int p = 0; p < c.world; ++p) {
+            const int64_t plo = (int64_t)p * per, phi = min(plo + per, n16);
+            for (int64_t i = plo + tid; i < phi; i += stride) my_slot[i] = data[i];
+        }
+        ar_barrier(c, flags_a, epoch);
+        const int64_t lo = (int64_t)c.rank * per, hi = min(lo + per, n16);
+        for (int64_t i = lo + tid; i < hi; i += stride) {
+            float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            for (int r = 0; r < c.world; ++r) acc_bf16x8(a, ld_cg_u4(reinterpret_cast<const uint4*>(c.peer[r] + slot_off) + i));
+            const uint4 v = pack_bf16x8(a);
+            my_slot[i] = v;                     // peers read the reduced part from here after barrier B
+            data[i] = v;
+        }
+        ar_barrier(c, flags_b, epoch);
+        for (int p = 0; p < c.world; ++p) {
+            if (p == c.rank) continue;
+            const int64_t plo = (int64_t)p * per, phi = min(plo + per, n16);
+            const uint4* src = reinterpret_cast<const uint4*>(c.peer[p] + slot_off);
+            for (int64_t i = plo + tid; i < phi; i += stride) data[i] = ld_cg_u4(src + i);
+        }
+    }
+    // last block out advances the epoch for the next launch (graph replays read it from device memory)
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(&c.epoch[1], 1u) == gridDim.x - 1) {
+            c.epoch[1] = 0;
+            __threadfence();
+            c.epoch[0] = epoch;
+        }
+    }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+size_t b200_ar_buffer_bytes(size_t max_msg_bytes) {
+    const size_t slot = (max_msg_bytes + 1023) / 1024 * 1024;
+    return 2 * slot + 2 * sizeof(uint32_t) * AR_MAX_WORLD * AR_BLOCKS;
+}
+
+int b200_ar_alloc(size_t bytes, void** dev_ptr, void* ipc_handle_out64) {
+    if (!dev_ptr || !ipc_handle_out64) return B200_ERR_NULL;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");
+    void* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaMemset(p, 0, bytes);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) return (int)e;
+    cudaIpcMemHandle_t h;
+    e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) return (int)e;
+    memcpy(ipc_handle_out64, &h, 64);
+    *dev_ptr = p;
+    return B200_OK;
+}
+
+int b200_ar_open(const void* ipc_handle64, void** peer_ptr) {
+    if (!ipc_handle64 || !peer_ptr) return B200_ERR_NULL;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, ipc_handle64, 64);
+    return (int)cudaIpcOpenMemHandle(peer_ptr, h, cudaIpcMemLazyEnablePeerAccess);
+}
+
+int b200_ar_create(int rank, int world, void* const* peer_ptrs, size_t max_msg_bytes, void** comm_out) {
+    if (!peer_ptrs || !comm_out) return B200_ERR_NULL;
+    if (world < 1 || world > AR_MAX_WORLD || rank < 0 || rank >= world) return B200_ERR_RANGE;
+    ArComm* c = new ArComm();
+    for (int r = 0; r < AR_MAX_WORLD; ++r) c->peer[r] = r < world ? (uint8_t*)peer_ptrs[r] : nullptr;
+    c->rank = rank; c->world = world;
+    c->slot_bytes = (max_msg_bytes + 1023) / 1024 * 1024;
+    cudaError_t e = cudaMalloc((void**)&c->epoch, 2 * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMemset(c->epoch, 0, 2 * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { delete c; return (int)e; }
+    *comm_out = c;
+    return B200_OK;
+}
+
+int b200_allreduce_bf16(void* comm, void* data, int64_t n_elems, int two_shot, void* stream) {
+    if (!comm || !data) return B200_ERR_NULL;
+    const ArComm* c = (const ArComm*)comm;
+    if (n_elems < 0 || (n_elems & 7) || (size_t)n_elems * 2 > c->slot_bytes) return B200_ERR_RANGE;
+    if (((uintptr_t)data & 15) != 0) return B200_ERR_ALIGN;
+    if (n_elems == 0) return B200_OK;
+    // Small messages are barrier-latency-bound: fewer blocks = fewer cross-GPU flags to exchange.  The grid
+    // depends only on n_elems, so it is the same on every rank (block b pairs with block b of the peers).
+    int64_t grid = (n_elems / 8 + 1023) / 1024;             // 16 KB of message per block
+    grid = grid < 1 ? 1 : (grid > AR_BLOCKS ? AR_BLOCKS : grid);
+    if (two_shot && c->world > 2)
+        allreduce_kernel<true><<<(int)grid, AR_THREADS, 0, (cudaStream_t)stream>>>(*c, (uint4*)data, n_elems / 8);
+    else
+        allreduce_kernel<false><<<(int)grid, AR_THREADS, 0, (cudaStream_t)stream>>>(*c, (uint4*)data, n_elems / 8);
+    return (int)cudaGetLastError();
+}
+
+}  // extern "C"

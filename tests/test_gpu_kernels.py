@@ -541,3 +541,34 @@ def test_decode_many_items_ragged_with_padding_rows(ops, Hq, Hkv, splits):
     for b, L in enumerate(lens):
         if L == 0:
             assert outs[0][b].abs().sum().item() == 0
+
+
+# ---------------------------------------------------------------------------- (f3) TP all-reduce
+def test_peer_memory_allreduce_world1_and_argument_errors(ops):
+    """Single-GPU slice of csrc/allreduce.cu (the multi-GPU parity run is tools/ar_check.py, results
+    under profiles/): a one-rank communicator must leave the data unchanged bit for bit over repeated
+    calls (slot alternation, device-side epoch), also under CUDA-graph replay, and reject messages
+    that do not fit."""
+    ar = ops.TpAllReduce(0, 1, 64 << 10, lambda mine: [mine])
+    x = torch.randn(3 * 4096, device="cuda").bfloat16()
+    want = x.clone()
+    for _ in range(5):
+        ar.all_reduce_(x)
+    assert torch.equal(x, want)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        ar.all_reduce_(x)
+    torch.cuda.current_stream().wait_stream(s)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        ar.all_reduce_(x)
+        ar.all_reduce_(x)
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(x, want)
+    assert not ar.fits(torch.zeros(64 << 10, device="cuda").bfloat16())        # 128 KB > 64 KB
+    assert not ar.fits(torch.zeros(12, device="cuda").bfloat16())              # not a multiple of 8 elements
+    with pytest.raises(RuntimeError):
+        ar.all_reduce_(torch.zeros(12, device="cuda").bfloat16())
