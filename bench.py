@@ -56,7 +56,7 @@ def peaks():
 
 
 class ClockSampler(threading.Thread):
-    """Samples SM clock + throttle reasons during the timed region (NVML, 100 ms)."""
+    """Samples SM clock + throttle reasons during the timed regions (NVML, every 4 ms)."""
 
     def __init__(self, index):
         super().__init__(daemon=True)
@@ -95,7 +95,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._stop_evt.wait(0.1)
+            self._stop_evt.wait(0.004)
 
     def finish(self):
         self._stop_evt.set()
@@ -213,8 +213,8 @@ def run_ours(args):
     sampler = ClockSampler(local)
     sampler.start()
     ms_total = timed(step_resident, args.steps)
-    clocks = sampler.finish()
     ms_e2e = timed(step_e2e, args.steps)
+    clocks = sampler.finish()                                  # covers both timed regions (resident + e2e)
 
     # dominant kernel alone (paged_decode_kernel [+ reduce when split]) on the launching stream
     def decode_only():
