@@ -361,10 +361,16 @@ class TpAllReduce:
 
 
 _TP_AR = None
-# Measured on B200 NVSwitch boxes (tools/ar_check.py, profiles/r1h_allreduce_tp{2,4}.json): the one-shot
-# kernel is ~2x faster than NCCL 2.28 up to 8-32 KB (9-10 us vs 13-19 us per graph-replayed call) and ties or
-# loses above (NCCL reduces in the switch), so only messages up to this size leave NCCL by default.
-AR_DEFAULT_MAX_BYTES = 32 << 10
+# Measured on B200 NVSwitch boxes against NCCL 2.28 (tools/ar_check.py, profiles/r1h_allreduce_tp{2,4}.json,
+# per CUDA-graph-replayed call): TP2 9.5 vs 13.4 us at 2 KB, 13.7 vs 17.2 at 64 KB, a tie at 512 KB, 23 vs 25 at
+# 2 MB; TP4 10-11 vs 19 us up to 8 KB, 16 vs 21 at 64 KB, 20.6 vs 23.3 at 512 KB, but 34 vs 30 at 2 MB (NCCL
+# reduces inside the switch).  So the cut-off depends on the group size; TP8 is not measured, its value is a
+# conservative extrapolation (one-shot traffic grows with world - 1).
+AR_DEFAULT_MAX_BYTES = {2: 4 << 20, 3: 512 << 10, 4: 512 << 10}
+
+
+def _ar_default_max_bytes(world: int) -> int:
+    return AR_DEFAULT_MAX_BYTES.get(world, 128 << 10)
 
 
 def tp_all_reduce_(t: torch.Tensor) -> torch.Tensor:
@@ -383,7 +389,7 @@ def tp_all_reduce_(t: torch.Tensor) -> torch.Tensor:
                 out = [None] * world
                 dist.all_gather_object(out, mine)
                 return out
-            _TP_AR = TpAllReduce(dist.get_rank(), world, int(os.environ.get("B200ATTN_AR_MAX_BYTES", AR_DEFAULT_MAX_BYTES)), gather)
+            _TP_AR = TpAllReduce(dist.get_rank(), world, int(os.environ.get("B200ATTN_AR_MAX_BYTES", _ar_default_max_bytes(world))), gather)
     if _TP_AR is not False and _TP_AR.fits(t):
         return _TP_AR.all_reduce_(t)
     dist.all_reduce(t)

@@ -9,8 +9,8 @@
 //   [ slot 0 | slot 1 | arrival flags A[world][blocks] | arrival flags B[world][blocks] ]
 //
 // One-shot (world == 2 or small messages): block b copies its share of the input into the local slot,
-// publishes "epoch" into flag A[me][b] of every peer (st.release.sys after a system fence), waits until
-// all peers' flags for block b arrived (ld.acquire.sys), then sums that share over all ranks' slots in
+// publishes "epoch" into flag A[me][b] of every peer (system fence, then a relaxed system-scope store), waits until
+// all peers' flags for block b arrived (relaxed polling, then a system fence), then sums that share over all ranks' slots in
 // rank order in fp32 and writes bf16 back in place.  Two-shot (larger messages, world > 2): after the
 // same first barrier a rank reduces only ITS 1/world of the message, writes the result into its own
 // slot, a second barrier (flags B) publishes it, and every rank gathers the reduced parts.  Either way
@@ -39,12 +39,15 @@ struct ArComm {
     uint32_t* epoch;                            // device: [0] = completed all-reduces, [1] = blocks done in this launch
 };
 
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+// The flag itself travels with relaxed system-scope accesses; ordering comes from ONE system fence before
+// the store (release) and ONE after the poll succeeds (acquire).  Acquire loads inside the spin loop would
+// pay a fence per iteration.
+__device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
     uint32_t v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
 
@@ -54,11 +57,12 @@ __device__ __forceinline__ void ar_barrier(const ArComm& c, size_t flags_off, ui
     if ((int)threadIdx.x < c.world) {
         __threadfence_system();
         uint32_t* theirs = reinterpret_cast<uint32_t*>(c.peer[threadIdx.x] + flags_off) + c.rank * AR_BLOCKS + blockIdx.x;
-        st_release_sys(theirs, epoch);
+        st_relaxed_sys(theirs, epoch);
         const uint32_t* mine = reinterpret_cast<const uint32_t*>(c.peer[c.rank] + flags_off) + threadIdx.x * AR_BLOCKS + blockIdx.x;
         uint32_t spins = 0;
-        while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0)
+        while ((int32_t)(ld_relaxed_sys(mine) - epoch) < 0)
             if (++spins > (1u << 27)) __trap();
+        __threadfence_system();
     }
     __syncthreads();
 }
