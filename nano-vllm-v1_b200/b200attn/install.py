@@ -87,7 +87,7 @@ def install(pointwise: bool = True, runner: bool = True) -> None:
         importlib.import_module("nanovllm.layers.layernorm").RMSNorm.forward = _rmsnorm_forward
         importlib.import_module("nanovllm.layers.rotary_embedding").RotaryEmbedding.forward = _rotary_forward
         importlib.import_module("nanovllm.layers.activation").SiluAndMul.forward = _silu_forward
-    if os.environ.get("B200ATTN_ALLREDUCE", "0") == "1":      # opt-in: measured neutral end to end
+    if os.environ.get("B200ATTN_ALLREDUCE", "1") != "0":      # B200ATTN_ALLREDUCE=0 keeps every all-reduce on NCCL
         from .layers.linear import row_parallel_forward
         importlib.import_module("nanovllm.layers.linear").RowParallelLinear.forward = row_parallel_forward
     if runner:

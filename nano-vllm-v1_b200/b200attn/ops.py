@@ -327,7 +327,7 @@ class TpAllReduce:
         import ctypes
         lib = load_library()
         self.rank, self.world, self.max_bytes = rank, world, max_bytes
-        self.two_shot_min_bytes = int(__import__("os").environ.get("B200ATTN_AR_TWO_SHOT_MIN", 256 * 1024))
+        self.two_shot_min_bytes = int(__import__("os").environ.get("B200ATTN_AR_TWO_SHOT_MIN", _ar_two_shot_min_bytes(world)))
         nbytes = lib.b200_ar_buffer_bytes(max_bytes)
         ptr, handle = ctypes.c_void_p(), ctypes.create_string_buffer(64)
         check(lib.b200_ar_alloc(nbytes, ctypes.byref(ptr), handle), "b200_ar_alloc")
@@ -361,16 +361,22 @@ class TpAllReduce:
 
 
 _TP_AR = None
-# Measured on B200 NVSwitch boxes against NCCL 2.28 (tools/ar_check.py, profiles/r1h_allreduce_tp{2,4}.json,
-# per CUDA-graph-replayed call): TP2 9.5 vs 13.4 us at 2 KB, 13.7 vs 17.2 at 64 KB, a tie at 512 KB, 23 vs 25 at
-# 2 MB; TP4 10-11 vs 19 us up to 8 KB, 16 vs 21 at 64 KB, 20.6 vs 23.3 at 512 KB, but 34 vs 30 at 2 MB (NCCL
-# reduces inside the switch).  So the cut-off depends on the group size; TP8 is not measured, its value is a
-# conservative extrapolation (one-shot traffic grows with world - 1).
-AR_DEFAULT_MAX_BYTES = {2: 4 << 20, 3: 512 << 10, 4: 512 << 10}
+# Measured on B200 NVSwitch boxes against NCCL 2.28 (tools/ar_check.py, profiles/r1h_allreduce_tp{2,4,8}.json,
+# per CUDA-graph-replayed call, us, ours vs NCCL):
+#   TP2  2 KB 9.5/13.4   64 KB 13.7/17.2   512 KB 17.9/17.7   2 MB 23.1/25.3   4 MB 32.7/43.0   (one-shot)
+#   TP4  2 KB 11.1/18.8  64 KB 17.6/21.1   512 KB 18.3/23.1   2 MB 26.4/29.3   4 MB 29.9/42.2   (two-shot from 2 MB)
+#   TP8  2 KB 13.8/29.0  64 KB 21.9/31.6   512 KB 26.4/33.9   2 MB 32.0/37.8   4 MB 38.3/58.4   (two-shot from 1 MB)
+# so every message up to the 4 MB slot takes the peer-memory kernel, and the two-shot form starts where its
+# second cross-GPU barrier (~8 us) is paid back by moving 2/world instead of (world-1) messages per rank.
+AR_DEFAULT_MAX_BYTES = 4 << 20
 
 
 def _ar_default_max_bytes(world: int) -> int:
-    return AR_DEFAULT_MAX_BYTES.get(world, 128 << 10)
+    return AR_DEFAULT_MAX_BYTES
+
+
+def _ar_two_shot_min_bytes(world: int) -> int:
+    return (2 << 20) if world <= 4 else (1 << 20)
 
 
 def tp_all_reduce_(t: torch.Tensor) -> torch.Tensor:

@@ -6,16 +6,16 @@
 // its peers map through CUDA IPC (NVSwitch gives every pair full bandwidth, so all traffic is direct
 // peer loads):
 //
-//   [ slot 0 | slot 1 | arrival flags A[world][blocks] | arrival flags B[world][blocks] ]
+//   [ slot 0 | slot 1 | arrival flags A[world] | arrival flags B[world] ]
 //
-// One-shot (world == 2 or small messages): block b copies its share of the input into the local slot,
-// publishes "epoch" into flag A[me][b] of every peer (system fence, then a relaxed system-scope store), waits until
-// all peers' flags for block b arrived (relaxed polling, then a system fence), then sums that share over all ranks' slots in
-// rank order in fp32 and writes bf16 back in place.  Two-shot (larger messages, world > 2): after the
-// same first barrier a rank reduces only ITS 1/world of the message, writes the result into its own
-// slot, a second barrier (flags B) publishes it, and every rank gathers the reduced parts.  Either way
-// all ranks add in the same order, so they hold bit-identical results (required: every rank samples
-// nothing, but all must feed identical activations to the next layer).
+// One-shot (world == 2 or small messages): every block copies its share of the input into the local slot, all
+// blocks of all ranks meet at a barrier, then each block sums its share over all ranks' slots in rank order in
+// fp32 and writes bf16 back in place.  Two-shot (larger messages, world > 2): after the same first barrier a
+// rank reduces only ITS 1/world of the message, writes the result into its own slot, a second barrier (flags B)
+// publishes it, and every rank gathers the reduced parts.  Either way all ranks add in the same order, so they
+// hold bit-identical results (every rank must feed identical activations to the next layer).
+// The barrier is hierarchical (ar_barrier): blocks of a rank meet on a local counter, block 0 alone exchanges
+// flags with the peers, then releases its siblings -- two system-scope fences per barrier per rank.
 // Slots alternate with the epoch, so a rank that runs ahead into the next all-reduce never overwrites
 // data a slower peer is still reading: it cannot pass that call's barrier before the peer got there.
 // The epoch lives in device memory and is advanced by the kernel itself (last block out), so a captured
@@ -29,14 +29,15 @@
 namespace b200 {
 
 constexpr int AR_MAX_WORLD = 8;
-constexpr int AR_BLOCKS = 48;                   // blocks per launch == barrier lanes per rank
+constexpr int AR_BLOCKS = 128;                  // most blocks per launch (all must be co-resident: they spin on each other)
 constexpr int AR_THREADS = 512;
 
 struct ArComm {
     uint8_t* peer[AR_MAX_WORLD];                // IPC-mapped buffers, peer[rank] is the local one
     int32_t rank, world;
     size_t slot_bytes;
-    uint32_t* epoch;                            // device: [0] = completed all-reduces, [1] = blocks done in this launch
+    uint32_t* epoch;                            // device: [0] = completed all-reduces, [1] = blocks done in this launch,
+                                                // [2],[3] = arrive counter / go flag of barrier A, [4],[5] = of barrier B
 };
 
 // The flag itself travels with relaxed system-scope accesses; ordering comes from ONE system fence before
@@ -51,18 +52,55 @@ __device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
     return v;
 }
 
-// All ranks' block b meet here.  `flags_off` selects flag set A or B inside each rank's buffer.
-__device__ __forceinline__ void ar_barrier(const ArComm& c, size_t flags_off, uint32_t epoch) {
-    __syncthreads();                            // this block's stores are ordered before the fence below
-    if ((int)threadIdx.x < c.world) {
-        __threadfence_system();
-        uint32_t* theirs = reinterpret_cast<uint32_t*>(c.peer[threadIdx.x] + flags_off) + c.rank * AR_BLOCKS + blockIdx.x;
-        st_relaxed_sys(theirs, epoch);
-        const uint32_t* mine = reinterpret_cast<const uint32_t*>(c.peer[c.rank] + flags_off) + threadIdx.x * AR_BLOCKS + blockIdx.x;
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// All blocks of all ranks meet here.  Hierarchical on purpose: a system-scope fence is a GPU-wide operation,
+// and one per block (48 blocks: +9 us measured) serialises; so the blocks of a rank first meet on a local
+// counter (gpu scope), block 0 alone talks to the peers (two system fences per barrier per rank), then
+// releases its siblings through a local flag.  `which` = 0 / 1 selects flag set A / B.
+__device__ __forceinline__ void ar_barrier(const ArComm& c, int which, size_t flags_off, uint32_t epoch) {
+    uint32_t* arrive = c.epoch + 2 + 2 * which;
+    uint32_t* go = arrive + 1;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();                        // this block's slot writes before its arrival
+        atomicAdd(arrive, 1u);
+    }
+    if (blockIdx.x == 0) {
+        if (threadIdx.x < 32) {
+            uint32_t spins = 0;
+            if (threadIdx.x == 0) {
+                while (ld_acquire_gpu(arrive) < gridDim.x)
+                    if (++spins > (1u << 27)) __trap();
+                __threadfence_system();         // everything this rank wrote is visible before the flags are
+            }
+            __syncwarp();
+            if ((int)threadIdx.x < c.world) {
+                uint32_t* theirs = reinterpret_cast<uint32_t*>(c.peer[threadIdx.x] + flags_off) + c.rank;
+                st_relaxed_sys(theirs, epoch);
+                const uint32_t* mine = reinterpret_cast<const uint32_t*>(c.peer[c.rank] + flags_off) + threadIdx.x;
+                spins = 0;
+                while ((int32_t)(ld_relaxed_sys(mine) - epoch) < 0)
+                    if (++spins > (1u << 27)) __trap();
+            }
+            __syncwarp();
+            if (threadIdx.x == 0) {
+                __threadfence_system();
+                st_release_gpu(go, epoch);
+            }
+        }
+    }
+    if (threadIdx.x == 0) {
         uint32_t spins = 0;
-        while ((int32_t)(ld_relaxed_sys(mine) - epoch) < 0)
+        while ((int32_t)(ld_acquire_gpu(go) - epoch) < 0)
             if (++spins > (1u << 27)) __trap();
-        __threadfence_system();
     }
     __syncthreads();
 }
@@ -86,15 +124,14 @@ template <bool TWO_SHOT>
 __global__ void __launch_bounds__(AR_THREADS) allreduce_kernel(const ArComm c, uint4* data, int64_t n16) {
     const uint32_t epoch = c.epoch[0] + 1;
     const size_t slot_off = (epoch & 1u) * c.slot_bytes;
-    const size_t flags_a = 2 * c.slot_bytes, flags_b = flags_a + sizeof(uint32_t) * AR_MAX_WORLD * AR_BLOCKS;
+    const size_t flags_a = 2 * c.slot_bytes, flags_b = flags_a + sizeof(uint32_t) * AR_MAX_WORLD;
     uint4* my_slot = reinterpret_cast<uint4*>(c.peer[c.rank] + slot_off);
     const int64_t stride = (int64_t)gridDim.x * AR_THREADS;
     const int64_t tid = (int64_t)blockIdx.x * AR_THREADS + threadIdx.x;
 
     if (!TWO_SHOT) {
-        // block b owns chunks {tid + k*stride}: the same set on every rank, so a per-block barrier suffices
         for (int64_t i = tid; i < n16; i += stride) my_slot[i] = data[i];
-        ar_barrier(c, flags_a, epoch);
+        ar_barrier(c, 0, flags_a, epoch);
         int64_t i = tid;
         for (; i + 3 * stride < n16; i += 4 * stride) {         // 4 x world independent 16-byte peer loads in flight
             uint4 v[4][AR_MAX_WORLD];
@@ -126,7 +163,7 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_kernel(const ArComm c, u
             const int64_t plo = (int64_t)p * per, phi = min(plo + per, n16);
             for (int64_t i = plo + tid; i < phi; i += stride) my_slot[i] = data[i];
         }
-        ar_barrier(c, flags_a, epoch);
+        ar_barrier(c, 0, flags_a, epoch);
         const int64_t lo = (int64_t)c.rank * per, hi = min(lo + per, n16);
         for (int64_t i = lo + tid; i < hi; i += stride) {
             float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -135,12 +172,18 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_kernel(const ArComm c, u
             my_slot[i] = v;                     // peers read the reduced part from here after barrier B
             data[i] = v;
         }
-        ar_barrier(c, flags_b, epoch);
-        for (int p = 0; p < c.world; ++p) {
-            if (p == c.rank) continue;
-            const int64_t plo = (int64_t)p * per, phi = min(plo + per, n16);
-            const uint4* src = reinterpret_cast<const uint4*>(c.peer[p] + slot_off);
-            for (int64_t i = plo + tid; i < phi; i += stride) data[i] = ld_cg_u4(src + i);
+        ar_barrier(c, 1, flags_b, epoch);
+        // gather: index i of my own part maps to i - lo + p*per in part p; all peers' loads of one step are
+        // issued before the first store (world - 1 independent round trips in flight per thread)
+        for (int64_t j = tid; j < per; j += stride) {
+            uint4 v[AR_MAX_WORLD];
+#pragma unroll
+            for (int p = 0; p < AR_MAX_WORLD; ++p)
+                if (p < c.world && p != c.rank && (int64_t)p * per + j < n16)
+                    v[p] = ld_cg_u4(reinterpret_cast<const uint4*>(c.peer[p] + slot_off) + (int64_t)p * per + j);
+#pragma unroll
+            for (int p = 0; p < AR_MAX_WORLD; ++p)
+                if (p < c.world && p != c.rank && (int64_t)p * per + j < n16) data[(int64_t)p * per + j] = v[p];
         }
     }
     // last block out advances the epoch for the next launch (graph replays read it from device memory)
@@ -149,6 +192,8 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_kernel(const ArComm c, u
         __threadfence();
         if (atomicAdd(&c.epoch[1], 1u) == gridDim.x - 1) {
             c.epoch[1] = 0;
+            c.epoch[2] = 0;                     // arrive counters of both barriers, for the next launch
+            c.epoch[4] = 0;
             __threadfence();
             c.epoch[0] = epoch;
         }
@@ -163,7 +208,7 @@ extern "C" {
 
 size_t b200_ar_buffer_bytes(size_t max_msg_bytes) {
     const size_t slot = (max_msg_bytes + 1023) / 1024 * 1024;
-    return 2 * slot + 2 * sizeof(uint32_t) * AR_MAX_WORLD * AR_BLOCKS;
+    return 2 * slot + 2 * sizeof(uint32_t) * AR_MAX_WORLD;
 }
 
 int b200_ar_alloc(size_t bytes, void** dev_ptr, void* ipc_handle_out64) {
@@ -198,8 +243,8 @@ int b200_ar_create(int rank, int world, void* const* peer_ptrs, size_t max_msg_b
     for (int r = 0; r < AR_MAX_WORLD; ++r) c->peer[r] = r < world ? (uint8_t*)peer_ptrs[r] : nullptr;
     c->rank = rank; c->world = world;
     c->slot_bytes = (max_msg_bytes + 1023) / 1024 * 1024;
-    cudaError_t e = cudaMalloc((void**)&c->epoch, 2 * sizeof(uint32_t));
-    if (e == cudaSuccess) e = cudaMemset(c->epoch, 0, 2 * sizeof(uint32_t));
+    cudaError_t e = cudaMalloc((void**)&c->epoch, 8 * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMemset(c->epoch, 0, 8 * sizeof(uint32_t));
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
     if (e != cudaSuccess) { delete c; return (int)e; }
     *comm_out = c;
@@ -212,11 +257,14 @@ int b200_allreduce_bf16(void* comm, void* data, int64_t n_elems, int two_shot, v
     if (n_elems < 0 || (n_elems & 7) || (size_t)n_elems * 2 > c->slot_bytes) return B200_ERR_RANGE;
     if (((uintptr_t)data & 15) != 0) return B200_ERR_ALIGN;
     if (n_elems == 0) return B200_OK;
-    // Small messages are barrier-latency-bound: fewer blocks = fewer cross-GPU flags to exchange.  The grid
-    // depends only on n_elems, so it is the same on every rank (block b pairs with block b of the peers).
-    int64_t grid = (n_elems / 8 + 1023) / 1024;             // 16 KB of message per block
+    // About four 16-byte chunks per thread in the phase that reads the peers (memory-level parallelism comes
+    // from the unrolled loads, not from long loops); the grid depends only on n_elems and the group size, so it
+    // is the same on every rank.  All blocks spin on each other, so the grid must stay co-resident (<= 128 < 148 SMs).
+    const bool two = two_shot && c->world > 2;
+    const int64_t work = two ? (n_elems / 8 + c->world - 1) / c->world : (n_elems / 8 + 3) / 4;   // chunks per thread-step
+    int64_t grid = (work + AR_THREADS - 1) / AR_THREADS;
     grid = grid < 1 ? 1 : (grid > AR_BLOCKS ? AR_BLOCKS : grid);
-    if (two_shot && c->world > 2)
+    if (two)
         allreduce_kernel<true><<<(int)grid, AR_THREADS, 0, (cudaStream_t)stream>>>(*c, (uint4*)data, n_elems / 8);
     else
         allreduce_kernel<false><<<(int)grid, AR_THREADS, 0, (cudaStream_t)stream>>>(*c, (uint4*)data, n_elems / 8);

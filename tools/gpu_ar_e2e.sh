@@ -1,7 +1,10 @@
 #!/bin/bash
-# TP2 end to end with (1) and without (0) the peer-memory all-reduce, then the parity/latency check.  2-GPU box.
+# Drop-in arm end to end with (1) and without (0) the peer-memory all-reduce at tensor-parallel degree $1.
+# Usage: bash tools/gpu_ar_e2e.sh TP [num_seqs] [tag]
+TP=${1:-2}; NS=${2:-256}; TAG=${3:-ar_e2e_tp${TP}_bs${NS}}
+mkdir -p gpurun_out
 for ar in 1 0; do
-  B200ATTN_ALLREDUCE=$ar timeout 600 python tools/e2e_generate.py --arm dropin --size 8b --tp 2 --num-seqs 4 --in-len 128 --out-len 256 --chunked-prefill --out gpurun_out/ar_e2e_tp2_ar${ar}.json > gpurun_out/ar_e2e_tp2_ar${ar}.log 2>&1
-  echo "ar=$ar exit $?"; tail -n 1 gpurun_out/ar_e2e_tp2_ar${ar}.log | cut -c1-400
+  B200ATTN_ALLREDUCE=$ar timeout 600 python tools/e2e_generate.py --arm dropin --size 8b --tp $TP --num-seqs $NS --in-len 128 --out-len 256 \
+    --chunked-prefill --out gpurun_out/${TAG}_ar${ar}.json > gpurun_out/${TAG}_ar${ar}.log 2>&1
+  echo "ar=$ar exit $?"; python -c "import json; d=json.load(open('gpurun_out/${TAG}_ar${ar}.json')); print('B200ATTN_ALLREDUCE=$ar tok/s', round(d['tok_per_s']), d['seconds_all'])"
 done
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/ar_check.py 2>&1 | grep -v Warn | tail -7
