@@ -56,8 +56,9 @@ int b200_sm_count(void);
  * reference's own process group), peers are mapped with b200_ar_open(), and b200_ar_create() builds the
  * communicator (peer_ptrs[rank] = the local buffer).  b200_allreduce_bf16 sums `data` (n_elems bf16,
  * multiple of 8, 16-byte aligned) over all ranks IN PLACE, one kernel launch, stream-ordered, CUDA-graph
- * capturable; all ranks must call it in the same order with the same n_elems.  two_shot != 0 selects the
- * reduce-scatter + all-gather form (world > 2), 0 the one-shot form.  Results are bit-identical on all ranks. */
+ * capturable; all ranks must call it in the same order with the same n_elems.  two_shot: 0 = one-shot, 1 = reduce-scatter +
+ * all-gather with peer loads, 2 = the same with peer stores (push), 3 = one-shot with
+ * peer stores (needs world x message <= 2 x max_msg_bytes); 1 and 2 need world > 2.  Results are bit-identical on all ranks. */
 size_t b200_ar_buffer_bytes(size_t max_msg_bytes);
 int b200_ar_alloc(size_t bytes, void** dev_ptr, void* ipc_handle_out64);
 int b200_ar_open(const void* ipc_handle64, void** peer_ptr);

@@ -327,6 +327,7 @@ class TpAllReduce:
         import ctypes
         lib = load_library()
         self.rank, self.world, self.max_bytes = rank, world, max_bytes
+        self.two_shot_form = int(__import__("os").environ.get("B200ATTN_AR_TWO_SHOT_FORM", 2))     # 1 = pull, 2 = push
         self.two_shot_min_bytes = int(__import__("os").environ.get("B200ATTN_AR_TWO_SHOT_MIN", _ar_two_shot_min_bytes(world)))
         nbytes = lib.b200_ar_buffer_bytes(max_bytes)
         ptr, handle = ctypes.c_void_p(), ctypes.create_string_buffer(64)
@@ -345,6 +346,14 @@ class TpAllReduce:
         check(lib.b200_ar_create(rank, world, peers, max_bytes, ctypes.byref(comm)), "b200_ar_create")
         self._comm, self._lib = comm, lib
 
+    def choose_form(self, nbytes: int) -> int:
+        """0 one-shot/pull, 1 two-shot/pull, 2 two-shot/push, 3 one-shot/push (include/b200attn.h)."""
+        if self.world > 2 and nbytes >= self.two_shot_min_bytes:
+            return self.two_shot_form
+        if nbytes * self.world <= 2 * self.max_bytes:           # every rank's copy fits one slot
+            return 3
+        return self.two_shot_form if self.world > 2 else 0
+
     def fits(self, t: torch.Tensor) -> bool:
         return (t.is_cuda and t.dtype == torch.bfloat16 and t.is_contiguous() and t.numel() % 8 == 0
                 and t.numel() * 2 <= self.max_bytes and t.data_ptr() % 16 == 0)
@@ -354,20 +363,20 @@ class TpAllReduce:
             raise RuntimeError("b200attn: tensor does not fit the peer-memory all-reduce (bf16, contiguous, "
                                f"numel % 8 == 0, <= {self.max_bytes} bytes)")
         if two_shot is None:
-            two_shot = self.world > 2 and t.numel() * 2 >= self.two_shot_min_bytes
-        check(self._lib.b200_allreduce_bf16(self._comm, t.data_ptr(), t.numel(), 1 if two_shot else 0, _stream()),
+            two_shot = self.choose_form(t.numel() * 2)
+        check(self._lib.b200_allreduce_bf16(self._comm, t.data_ptr(), t.numel(), int(two_shot), _stream()),
               "b200_allreduce_bf16")
         return t
 
 
 _TP_AR = None
 # Measured on B200 NVSwitch boxes against NCCL 2.28 (tools/ar_check.py, profiles/r1h_allreduce_tp{2,4,8}.json,
-# per CUDA-graph-replayed call, us, ours vs NCCL):
-#   TP2  2 KB 9.5/13.4   64 KB 13.7/17.2   512 KB 17.9/17.7   2 MB 23.1/25.3   4 MB 32.7/43.0   (one-shot)
-#   TP4  2 KB 11.1/18.8  64 KB 17.6/21.1   512 KB 18.3/23.1   2 MB 26.4/29.3   4 MB 29.9/42.2   (two-shot from 2 MB)
-#   TP8  2 KB 13.8/29.0  64 KB 21.9/31.6   512 KB 26.4/33.9   2 MB 32.0/37.8   4 MB 38.3/58.4   (two-shot from 1 MB)
-# so every message up to the 4 MB slot takes the peer-memory kernel, and the two-shot form starts where its
-# second cross-GPU barrier (~8 us) is paid back by moving 2/world instead of (world-1) messages per rank.
+# per CUDA-graph-replayed call, us, the form this module picks vs NCCL):
+#   TP2  8 KB 10.0/14.4   64 KB 13.2/17.1   512 KB 13.9/18.4   2 MB 15.7/25.3   4 MB 19.0/43.7   (one-shot push)
+#   TP4  8 KB 10.6/19.3   64 KB 15.2/21.2   512 KB 16.2/23.4   2 MB 23.1/30.4   4 MB 29.7/42.4   (one-shot push; 4 MB two-shot push)
+#   TP8  8 KB 12.4/30.2   64 KB 19.1/32.1   512 KB 20.4/34.2   2 MB 27.3/38.1   4 MB 34.0/58.6   (one-shot push; two-shot push from 1 MB)
+# Peer stores are posted, peer loads are round trips, so the push forms beat the pull forms by 2-6 us everywhere;
+# the two-shot form pays a second cross-GPU barrier (~8 us) and wins once (world-1) x message no longer fits.
 AR_DEFAULT_MAX_BYTES = 4 << 20
 
 
@@ -376,7 +385,7 @@ def _ar_default_max_bytes(world: int) -> int:
 
 
 def _ar_two_shot_min_bytes(world: int) -> int:
-    return (2 << 20) if world <= 4 else (1 << 20)
+    return (4 << 20) if world <= 4 else (1 << 20)
 
 
 def tp_all_reduce_(t: torch.Tensor) -> torch.Tensor:

@@ -200,6 +200,95 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_kernel(const ArComm c, u
     }
 }
 
+// Two-shot, PUSH form (two_shot == 2).  Remote stores are posted, remote loads are round trips: instead of
+// parking the input locally and letting the peers pull, a rank scatters part p of its input straight into
+// rank p's slot, reduces its own part from LOCAL memory after barrier A, broadcasts the reduced part into every
+// rank's result region, and after barrier B copies the result region out locally.
+// slot = [ contributions: world x per chunks | results: n16 chunks ]   (slot_bytes = 2 x the largest message)
+__global__ void __launch_bounds__(AR_THREADS) allreduce_push_kernel(const ArComm c, uint4* data, int64_t n16) {
+    const uint32_t epoch = c.epoch[0] + 1;
+    const size_t slot_off = (epoch & 1u) * c.slot_bytes;
+    const size_t flags_a = 2 * c.slot_bytes, flags_b = flags_a + sizeof(uint32_t) * AR_MAX_WORLD;
+    const int64_t stride = (int64_t)gridDim.x * AR_THREADS;
+    const int64_t tid = (int64_t)blockIdx.x * AR_THREADS + threadIdx.x;
+    const int64_t per = (n16 + c.world - 1) / c.world;
+    const size_t res_off = slot_off + c.slot_bytes / 2;
+
+    for (int64_t j = tid; j < per; j += stride) {
+        uint4 v[AR_MAX_WORLD];
+#pragma unroll
+        for (int p = 0; p < AR_MAX_WORLD; ++p)
+            if (p < c.world && (int64_t)p * per + j < n16) v[p] = data[(int64_t)p * per + j];
+#pragma unroll
+        for (int p = 0; p < AR_MAX_WORLD; ++p)
+            if (p < c.world && (int64_t)p * per + j < n16)
+                reinterpret_cast<uint4*>(c.peer[p] + slot_off)[(int64_t)c.rank * per + j] = v[p];
+    }
+    ar_barrier(c, 0, flags_a, epoch);
+    const uint4* contrib = reinterpret_cast<const uint4*>(c.peer[c.rank] + slot_off);
+    for (int64_t j = tid; j < per && (int64_t)c.rank * per + j < n16; j += stride) {
+        float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int r = 0; r < AR_MAX_WORLD; ++r)
+            if (r < c.world) acc_bf16x8(a, ld_cg_u4(contrib + (int64_t)r * per + j));
+        const uint4 v = pack_bf16x8(a);
+#pragma unroll
+        for (int q = 0; q < AR_MAX_WORLD; ++q)
+            if (q < c.world) reinterpret_cast<uint4*>(c.peer[q] + res_off)[(int64_t)c.rank * per + j] = v;
+    }
+    ar_barrier(c, 1, flags_b, epoch);
+    const uint4* res = reinterpret_cast<const uint4*>(c.peer[c.rank] + res_off);
+    for (int64_t i = tid; i < n16; i += stride) data[i] = ld_cg_u4(res + i);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(&c.epoch[1], 1u) == gridDim.x - 1) {
+            c.epoch[1] = 0;
+            c.epoch[2] = 0;
+            c.epoch[4] = 0;
+            __threadfence();
+            c.epoch[0] = epoch;
+        }
+    }
+}
+
+// One-shot, PUSH form (two_shot == 3): every rank stores its whole message into slot region [rank] of every
+// peer (posted stores), ONE barrier, then each rank sums its `world` local copies.  No remote loads at all;
+// needs world x message <= slot.
+__global__ void __launch_bounds__(AR_THREADS) allreduce_push1_kernel(const ArComm c, uint4* data, int64_t n16) {
+    const uint32_t epoch = c.epoch[0] + 1;
+    const size_t slot_off = (epoch & 1u) * c.slot_bytes;
+    const size_t flags_a = 2 * c.slot_bytes;
+    const int64_t stride = (int64_t)gridDim.x * AR_THREADS;
+    const int64_t tid = (int64_t)blockIdx.x * AR_THREADS + threadIdx.x;
+    for (int64_t i = tid; i < n16; i += stride) {
+        const uint4 v = data[i];
+#pragma unroll
+        for (int q = 0; q < AR_MAX_WORLD; ++q)
+            if (q < c.world) reinterpret_cast<uint4*>(c.peer[q] + slot_off)[(int64_t)c.rank * n16 + i] = v;
+    }
+    ar_barrier(c, 0, flags_a, epoch);
+    const uint4* mine = reinterpret_cast<const uint4*>(c.peer[c.rank] + slot_off);
+    for (int64_t i = tid; i < n16; i += stride) {
+        float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int r = 0; r < AR_MAX_WORLD; ++r)
+            if (r < c.world) acc_bf16x8(a, ld_cg_u4(mine + (int64_t)r * n16 + i));
+        data[i] = pack_bf16x8(a);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(&c.epoch[1], 1u) == gridDim.x - 1) {
+            c.epoch[1] = 0;
+            c.epoch[2] = 0;
+            c.epoch[4] = 0;
+            __threadfence();
+            c.epoch[0] = epoch;
+        }
+    }
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -207,7 +296,7 @@ using namespace b200;
 extern "C" {
 
 size_t b200_ar_buffer_bytes(size_t max_msg_bytes) {
-    const size_t slot = (max_msg_bytes + 1023) / 1024 * 1024;
+    const size_t slot = 2 * ((max_msg_bytes + 1023) / 1024 * 1024);   // contributions | results (push form)
     return 2 * slot + 2 * sizeof(uint32_t) * AR_MAX_WORLD;
 }
 
@@ -242,7 +331,7 @@ int b200_ar_create(int rank, int world, void* const* peer_ptrs, size_t max_msg_b
     ArComm* c = new ArComm();
     for (int r = 0; r < AR_MAX_WORLD; ++r) c->peer[r] = r < world ? (uint8_t*)peer_ptrs[r] : nullptr;
     c->rank = rank; c->world = world;
-    c->slot_bytes = (max_msg_bytes + 1023) / 1024 * 1024;
+    c->slot_bytes = 2 * ((max_msg_bytes + 1023) / 1024 * 1024);
     cudaError_t e = cudaMalloc((void**)&c->epoch, 8 * sizeof(uint32_t));
     if (e == cudaSuccess) e = cudaMemset(c->epoch, 0, 8 * sizeof(uint32_t));
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
@@ -254,17 +343,22 @@ int b200_ar_create(int rank, int world, void* const* peer_ptrs, size_t max_msg_b
 int b200_allreduce_bf16(void* comm, void* data, int64_t n_elems, int two_shot, void* stream) {
     if (!comm || !data) return B200_ERR_NULL;
     const ArComm* c = (const ArComm*)comm;
-    if (n_elems < 0 || (n_elems & 7) || (size_t)n_elems * 2 > c->slot_bytes) return B200_ERR_RANGE;
+    if (n_elems < 0 || (n_elems & 7) || (size_t)n_elems * 2 > c->slot_bytes / 2) return B200_ERR_RANGE;
     if (((uintptr_t)data & 15) != 0) return B200_ERR_ALIGN;
     if (n_elems == 0) return B200_OK;
     // About four 16-byte chunks per thread in the phase that reads the peers (memory-level parallelism comes
     // from the unrolled loads, not from long loops); the grid depends only on n_elems and the group size, so it
     // is the same on every rank.  All blocks spin on each other, so the grid must stay co-resident (<= 128 < 148 SMs).
-    const bool two = two_shot && c->world > 2;
+    const bool two = (two_shot == 1 || two_shot == 2) && c->world > 2;
     const int64_t work = two ? (n_elems / 8 + c->world - 1) / c->world : (n_elems / 8 + 3) / 4;   // chunks per thread-step
     int64_t grid = (work + AR_THREADS - 1) / AR_THREADS;
     grid = grid < 1 ? 1 : (grid > AR_BLOCKS ? AR_BLOCKS : grid);
-    if (two)
+    if (two_shot == 3) {
+        if ((size_t)n_elems * 2 * c->world > c->slot_bytes) return B200_ERR_RANGE;
+        allreduce_push1_kernel<<<(int)grid, AR_THREADS, 0, (cudaStream_t)stream>>>(*c, (uint4*)data, n_elems / 8);
+    } else if (two && two_shot == 2)
+        allreduce_push_kernel<<<(int)grid, AR_THREADS, 0, (cudaStream_t)stream>>>(*c, (uint4*)data, n_elems / 8);
+    else if (two)
         allreduce_kernel<true><<<(int)grid, AR_THREADS, 0, (cudaStream_t)stream>>>(*c, (uint4*)data, n_elems / 8);
     else
         allreduce_kernel<false><<<(int)grid, AR_THREADS, 0, (cudaStream_t)stream>>>(*c, (uint4*)data, n_elems / 8);

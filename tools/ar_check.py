@@ -27,7 +27,7 @@ ar = ops._TP_AR
 assert ar is not False and ar is not None
 sizes = [8, 1024, 4096, 8 * 4096, 64 * 4096, 256 * 4096, 512 * 4096]      # elements; 256 x 4096 = decode bs 256, 8B
 for n in sizes:
-    for two_shot in ([False, True] if world > 2 else [False]):
+    for two_shot in ([0, 1, 2, 3] if world > 2 else [0, 3]):
         for rep in range(3):                                               # repeats exercise slot alternation
             g = torch.Generator(device=dev).manual_seed(1000 * rank + n % 997 + rep)
             x = torch.randn(n, generator=g, device=dev, dtype=torch.bfloat16)
@@ -37,6 +37,8 @@ for n in sizes:
             for t in allx:
                 acc += t.float()
             want = acc.bfloat16()
+            if two_shot == 3 and 2 * n * world > 2 * ar.max_bytes:
+                continue
             got = ar.all_reduce_(x.clone(), two_shot=two_shot)
             same = [torch.empty_like(got) for _ in range(world)]
             dist.all_gather(same, got)
@@ -77,9 +79,12 @@ def graph_time(fn, x, iters=20, reps=20):
 for n in sizes[1:]:
     x = torch.zeros(n, dtype=torch.bfloat16, device=dev)
     rec = {"elems": n, "bytes": 2 * n, "nccl_us": graph_time(lambda t: dist.all_reduce(t), x),
-           "one_shot_us": graph_time(lambda t: ar.all_reduce_(t, two_shot=False), x)}
+           "one_shot_us": graph_time(lambda t: ar.all_reduce_(t, two_shot=0), x)}
+    if 2 * n * world <= 2 * ar.max_bytes:
+        rec["one_shot_push_us"] = graph_time(lambda t: ar.all_reduce_(t, two_shot=3), x)
     if world > 2:
-        rec["two_shot_us"] = graph_time(lambda t: ar.all_reduce_(t, two_shot=True), x)
+        rec["two_shot_us"] = graph_time(lambda t: ar.all_reduce_(t, two_shot=1), x)
+        rec["two_shot_push_us"] = graph_time(lambda t: ar.all_reduce_(t, two_shot=2), x)
     results.append(rec)
     if rank == 0:
         print(json.dumps(rec), flush=True)
