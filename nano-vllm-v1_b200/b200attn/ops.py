@@ -317,6 +317,16 @@ def silu_and_mul(x: torch.Tensor) -> torch.Tensor:
 
 
 # ---------------------------------------------------------------------------- (f3) TP all-reduce
+def ar_choose_form(world: int, nbytes: int, max_bytes: int, two_shot_min_bytes: int, two_shot_form: int = 2) -> int:
+    """Which form of csrc/allreduce.cu carries a message (include/b200attn.h: 0 one-shot/pull, 1 two-shot/pull,
+    2 two-shot/push, 3 one-shot/push).  Pure function of sizes, so every rank picks the same."""
+    if world > 2 and nbytes >= two_shot_min_bytes:
+        return two_shot_form
+    if nbytes * world <= 2 * max_bytes:                         # every rank's copy fits one slot
+        return 3
+    return two_shot_form if world > 2 else 0
+
+
 class TpAllReduce:
     """Small-message all-reduce over NVLink peer memory (csrc/allreduce.cu) for the partial sums of
     RowParallelLinear (nanovllm/layers/linear.py:407-410).  One instance per process; the IPC handles
@@ -347,12 +357,7 @@ class TpAllReduce:
         self._comm, self._lib = comm, lib
 
     def choose_form(self, nbytes: int) -> int:
-        """0 one-shot/pull, 1 two-shot/pull, 2 two-shot/push, 3 one-shot/push (include/b200attn.h)."""
-        if self.world > 2 and nbytes >= self.two_shot_min_bytes:
-            return self.two_shot_form
-        if nbytes * self.world <= 2 * self.max_bytes:           # every rank's copy fits one slot
-            return 3
-        return self.two_shot_form if self.world > 2 else 0
+        return ar_choose_form(self.world, nbytes, self.max_bytes, self.two_shot_min_bytes, self.two_shot_form)
 
     def fits(self, t: torch.Tensor) -> bool:
         return (t.is_cuda and t.dtype == torch.bfloat16 and t.is_contiguous() and t.numel() % 8 == 0
@@ -395,6 +400,8 @@ def tp_all_reduce_(t: torch.Tensor) -> torch.Tensor:
     import os
     import torch.distributed as dist
     global _TP_AR
+    if not t.is_cuda:
+        raise RuntimeError("b200attn: tp_all_reduce_ needs a CUDA tensor (no CPU fallback on this path)")
     if _TP_AR is None:
         world = dist.get_world_size()
         if world > 8:

@@ -350,6 +350,9 @@ int b200_allreduce_bf16(void* comm, void* data, int64_t n_elems, int two_shot, v
     // from the unrolled loads, not from long loops); the grid depends only on n_elems and the group size, so it
     // is the same on every rank.  All blocks spin on each other, so the grid must stay co-resident (<= 128 < 148 SMs).
     const bool two = (two_shot == 1 || two_shot == 2) && c->world > 2;
+    // push form: world x ceil(n16 / world) chunks of contributions must stay inside the first half of a slot
+    // (only the largest message with a group size that does not divide it can miss by world - 1 chunks)
+    if (two && two_shot == 2 && (size_t)((n_elems / 8 + c->world - 1) / c->world) * c->world * 16 > c->slot_bytes / 2) two_shot = 1;
     const int64_t work = two ? (n_elems / 8 + c->world - 1) / c->world : (n_elems / 8 + 3) / 4;   // chunks per thread-step
     int64_t grid = (work + AR_THREADS - 1) / AR_THREADS;
     grid = grid < 1 ? 1 : (grid > AR_BLOCKS ? AR_BLOCKS : grid);

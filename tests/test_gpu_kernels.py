@@ -554,6 +554,8 @@ def test_peer_memory_allreduce_world1_and_argument_errors(ops):
     want = x.clone()
     for _ in range(5):
         ar.all_reduce_(x)
+    for form in (0, 3, 1, 2):                                   # 1 and 2 degrade to one-shot when world <= 2
+        ar.all_reduce_(x, two_shot=form)
     assert torch.equal(x, want)
     s = torch.cuda.Stream()
     s.wait_stream(torch.cuda.current_stream())

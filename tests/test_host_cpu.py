@@ -193,3 +193,18 @@ def test_tp_control_plane_ships_the_packed_arena(path, monkeypatch):
     # other methods are forwarded untouched
     ours.call(r0, "exit", _reference_call=lambda self, name, *a: fell.append(name))
     assert fell == ["run", "exit"]
+
+
+def test_allreduce_form_policy_and_no_cpu_fallback():
+    """Host logic of the f3 all-reduce (b200attn/ops.py): the form is a pure function of sizes (every rank
+    must pick the same), follows the measured policy, and the entry point refuses CPU tensors."""
+    import torch
+    from b200attn import ops
+    MB = 1 << 20
+    pick = lambda world, nbytes: ops.ar_choose_form(world, nbytes, 4 * MB, ops._ar_two_shot_min_bytes(world))  # noqa: E731
+    assert pick(2, 8192) == 3 and pick(2, 4 * MB) == 3                    # TP2: one-shot push always fits
+    assert pick(4, 2 * MB) == 3 and pick(4, 4 * MB) == 2                  # TP4: 4 x 4 MB no longer fits a slot
+    assert pick(8, 512 << 10) == 3 and pick(8, MB) == 2 and pick(8, 2 * MB) == 2
+    assert ops.ar_choose_form(2, 8 * MB, 4 * MB, 16 * MB) == 0            # a 2-rank message too big to push: pull
+    with pytest.raises(RuntimeError):
+        ops.tp_all_reduce_(torch.zeros(8, dtype=torch.bfloat16))
