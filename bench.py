@@ -268,7 +268,7 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
-def prefill_leg(ops, device, hq, hkv, scale, timed, world, seqs=4, seqlen=4096, iters=5):
+def prefill_leg(ops, device, hq, hkv, scale, timed, world, seqs=4, seqlen=4096, iters=20):
     """Second half of BASELINE.json's metric ("prefill TFLOP/s"): the persistent tcgen05 prefill kernel on
     `seqs` x `seqlen` causal self-attention at this rank's head counts (unpaged form, attention.py:242-248).
     flops = 4*D*Hq*sum_b Lq(Lq+1)/2.  Peak = measured bf16 burst (MEASURED_PEAKS.json)."""
@@ -283,7 +283,7 @@ def prefill_leg(ops, device, hq, hkv, scale, timed, world, seqs=4, seqlen=4096, 
 
     def run():
         ops.attn_varlen_planned(q, k, v, cu, cu, seqlen, seqlen, scale, plan=plan, out=out)
-    for _ in range(3):
+    for _ in range(5):
         run()
     ms = timed(run, iters) / iters
     flops = 4 * D * hq * seqs * (seqlen * (seqlen + 1) // 2)
