@@ -64,6 +64,36 @@ int b200_ar_alloc(size_t bytes, void** dev_ptr, void* ipc_handle_out64);
 int b200_ar_open(const void* ipc_handle64, void** peer_ptr);
 int b200_ar_create(int rank, int world, void* const* peer_ptrs, size_t max_msg_bytes, void** comm_out);
 int b200_allreduce_bf16(void* comm, void* data, int64_t n_elems, int two_shot, void* stream);
+/* Tear-down, the counterpart of the reference's dist.destroy_process_group (engine/model_runner.py:187-193):
+ * closes the peers' IPC mappings, frees the local buffer (from b200_ar_alloc) and the communicator.  Synchronise
+ * the device and the group first.  b200_ar_status: 0 = healthy, 1 = a wait inside some launch exceeded
+ * B200ATTN_AR_TIMEOUT_S (default 30 s): the kernels give up and flag it instead of trapping the context;
+ * synchronises the device (tests, tools, shutdown).  All launches are cooperative (co-resident blocks). */
+int b200_ar_destroy(void* comm);
+int b200_ar_status(void* comm, int32_t* status_out);
+
+/* ---- (f3) all-reduce FUSED with the residual add + RMSNorm that follows it, on NVLS multicast memory ----
+ * Replaces, in ONE launch per rank, dist.all_reduce(y) of RowParallelLinear.forward (layers/linear.py:407-410)
+ * AND the RMSNorm.add_rms_forward that consumes y (layers/layernorm.py:95-141, called at models/qwen3.py:370,374,440):
+ *     s        = sum over ranks of x            (in-switch: multimem.ld_reduce, fp32 accumulate, one bf16 rounding,
+ *                                                 i.e. the value dist.all_reduce would have produced)
+ *     v        = float(s) + float(residual);   residual <- bf16(v)           (in place)
+ *     out      = bf16( bf16(v * rsqrt(mean(v^2) + eps)) * weight )
+ * `local_buf` / `multicast_buf`: the unicast and the multicast mapping of ONE symmetric allocation of
+ * b200_nvls_buffer_bytes(max_msg_bytes) bytes per rank (cuMemCreate + cuMulticastBindMem; the drop-in gets both
+ * from torch.distributed._symmetric_memory on the reference's own process group).  world == 1 needs no multicast
+ * mapping (pass NULL).  After b200_nvls_create on every rank the host must run a group barrier before the first
+ * call.  x [T, hidden] bf16: this rank's partial sums (any device memory); residual [T, hidden] bf16 updated in
+ * place, or NULL (then v = float(s)); weight [hidden] bf16, or NULL together with residual for a plain all-reduce
+ * (out <- s).  one_shot != 0: every rank reduces every row itself (one barrier; small messages); 0: reduce-scatter
+ * + multicast all-gather inside the kernel (two barriers).  All ranks must pass the same shapes and form.
+ * Stream-ordered, CUDA-graph capturable (slots alternate with a device-resident epoch), cooperative launch. */
+size_t b200_nvls_buffer_bytes(size_t max_msg_bytes);
+int b200_nvls_create(int rank, int world, void* local_buf, void* multicast_buf, size_t max_msg_bytes, void** comm_out);
+int b200_nvls_allreduce_add_rmsnorm(void* comm, const void* x, void* residual, const void* weight, float eps, void* out,
+                                    int32_t num_tokens, int32_t hidden, int32_t one_shot, void* stream);
+int b200_nvls_status(void* comm, int32_t* status_out);
+int b200_nvls_destroy(void* comm);
 
 /* Debug/profiling aid (no reference counterpart): while `dev_buf` (zeroed int64[4][max_tiles][8] in
  * device memory) is non-NULL, b200_attn_prefill_planned runs an instrumented build whose CTA 0 stamps
@@ -95,8 +125,14 @@ int b200_kv_scatter(const void* key, const void* value,
  *     the context (-1 eager, 0 graph) are never dereferenced.
  *     num_splits: from b200_decode_plan (host-only heuristic => static under CUDA graphs).
  *     workspace: b200_decode_workspace_bytes(B, Hq, num_splits) bytes, may be NULL iff
- *     num_splits == 1.
+ *     num_splits == 1.  Its first B200_DECODE_TICKET_BYTES bytes are arrival tickets (one int32 per
+ *     (row, kv head)): they must be ZERO before the first launch that uses the buffer and every launch
+ *     leaves them zero, so one zero-initialised buffer serves all calls and CUDA-graph replays.  The
+ *     split that arrives last at a (row, kv head) merges all of them with LSE weights inside the same
+ *     launch; there is no separate reduce launch (B200ATTN_DECODE_FUSED_REDUCE=0 restores it; it is
+ *     also used when B * Hkv tickets do not fit the region).
  */
+#define B200_DECODE_TICKET_BYTES (64 * 1024)
 int b200_decode_plan(int32_t batch, int32_t num_kv_heads, int32_t max_context_len);
 size_t b200_decode_workspace_bytes(int32_t batch, int32_t num_heads, int32_t num_splits);
 int b200_attn_decode(const void* q, int64_t q_token_stride,

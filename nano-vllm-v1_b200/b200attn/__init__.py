@@ -4,11 +4,12 @@ Thin Python over the C ABI in include/b200attn.h (libb200attn.so, hand-written C
 Module layout mirrors the reference so parity tests read like the reference's call sites:
 
     b200attn.layers.attention          <- nanovllm/layers/attention.py   (Attention, store_kvcache)
-    b200attn.layers.layernorm          <- nanovllm/layers/layernorm.py   (RMSNorm)
-    b200attn.layers.rotary_embedding   <- nanovllm/layers/rotary_embedding.py (RotaryEmbedding, get_rope)
-    b200attn.layers.activation         <- nanovllm/layers/activation.py  (SiluAndMul)
+    b200attn.layers.linear             <- nanovllm/layers/linear.py      (RowParallelLinear.forward, f3)
     b200attn.utils.context             <- nanovllm/utils/context.py      (Context, get/set/reset_context)
-    b200attn.install                   patches an importable `nanovllm` in place (drop-in)
+    b200attn.engine.model_runner       <- nanovllm/engine/model_runner.py (the in-scope ModelRunner methods)
+    b200attn.install                   patches an importable `nanovllm` in place (drop-in): RMSNorm,
+                                       RotaryEmbedding and SiluAndMul forward are bound onto the
+                                       reference's own classes there, straight to b200attn.ops
 
 There is NO CPU fallback, no Triton and no flash-attn on this path: if the CUDA library is
 missing or a tensor is not on a CUDA device the ops raise.

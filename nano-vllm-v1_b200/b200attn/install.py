@@ -9,7 +9,11 @@ stay valid whatever was imported first:
     nanovllm.models.qwen3.Qwen3Attention.forward       -> qkv_proj, ONE fused q/k-norm+RoPE+KV-scatter launch,
                                                           attention, o_proj (qwen3.py:183-199 order kept;
                                                           B200ATTN_FUSE_STORE=0 keeps the scatter separate)
-    nanovllm.layers.layernorm.RMSNorm.forward          -> b200_rmsnorm (fused residual add)
+    nanovllm.layers.layernorm.RMSNorm.forward          -> b200_rmsnorm (fused residual add), or -- when its input is the
+                                                          pending output of a RowParallelLinear -- the NVLS launch that
+                                                          all-reduces, adds the residual and normalises in one go
+    nanovllm.layers.linear.RowParallelLinear.forward   -> peer-memory all-reduce / deferred to that RMSNorm launch
+    nanovllm.models.qwen3.Qwen3Model.forward           -> same code, wrapped in ops.deferred_all_reduce()
     nanovllm.layers.rotary_embedding.RotaryEmbedding.forward -> rotation-only kernel
     nanovllm.layers.activation.SiluAndMul.forward      -> b200_silu_and_mul
     nanovllm.engine.model_runner.ModelRunner.{allocate_kv_cache, prepare_model_input, run, call, run_packed}
@@ -57,10 +61,18 @@ def _qwen3_attention_forward(self, positions, hidden_states):
 
 
 def _rmsnorm_forward(self, x, residual=None):
-    xc = x if x.is_contiguous() else x.contiguous()
     if residual is None:
-        return ops.rms_norm(xc, self.weight, self.eps)
-    return ops.rms_norm(xc, self.weight, self.eps, residual if residual.is_contiguous() else residual.contiguous())
+        ops.flush_pending_all_reduce()
+        return ops.rms_norm(x if x.is_contiguous() else x.contiguous(), self.weight, self.eps)
+    # x may be the un-reduced output of the RowParallelLinear in front (ops.tp_row_parallel_output): the
+    # all-reduce then runs inside this launch
+    return ops.tp_add_rms_norm(x if x.is_contiguous() else x.contiguous(), residual if residual.is_contiguous() else residual.contiguous(),
+                               self.weight, self.eps)
+
+
+def _qwen3_model_forward(self, input_ids, positions, _reference_forward=None):
+    with ops.deferred_all_reduce():
+        return _reference_forward(self, input_ids, positions)
 
 
 def _rotary_forward(self, positions, query, key):
@@ -90,6 +102,11 @@ def install(pointwise: bool = True, runner: bool = True) -> None:
     if os.environ.get("B200ATTN_ALLREDUCE", "1") != "0":      # B200ATTN_ALLREDUCE=0 keeps every all-reduce on NCCL
         from .layers.linear import row_parallel_forward
         importlib.import_module("nanovllm.layers.linear").RowParallelLinear.forward = row_parallel_forward
+        if pointwise:                                          # the fused form needs our RMSNorm.forward on the other end
+            qwen3 = importlib.import_module("nanovllm.models.qwen3")
+            ref_model_forward = qwen3.Qwen3Model.forward
+            qwen3.Qwen3Model.forward = lambda self, input_ids, positions: _qwen3_model_forward(
+                self, input_ids, positions, _reference_forward=ref_model_forward)
     if runner:
         from .engine import model_runner as ours
         mr = importlib.import_module("nanovllm.engine.model_runner")

@@ -52,34 +52,41 @@ def store_kvcache(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor,
 
 
 # ------------------------------------------------------------------------------------ (3)
-class DecodeWorkspace:
-    """Split-K partials, allocated once (allocate_kv_cache time) and reused by every layer."""
-
-    def __init__(self, max_batch: int, num_heads: int, max_splits: int, device) -> None:
-        lib = load_library()
-        self.max_batch, self.num_heads, self.max_splits = max_batch, num_heads, max_splits
-        nbytes = lib.b200_decode_workspace_bytes(max_batch, num_heads, max(max_splits, 2))
-        self.buf = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=device)
-
-    def fits(self, batch: int, num_heads: int, splits: int) -> bool:
-        return load_library().b200_decode_workspace_bytes(batch, num_heads, splits) <= self.buf.numel()
-
-
 _WS_CACHE = {}
+_WS_RETIRED = []        # superseded workspaces: CUDA graphs captured earlier still hold their raw pointers
+
+
+def _device_key(device) -> int:
+    device = torch.device(device)
+    return device.index if device.index is not None else torch.cuda.current_device()
+
+
+def _grow_workspace(key: int, nbytes: int, device) -> torch.Tensor:
+    """Replace the per-device workspace by a larger one.  The old buffer is RETIRED, never freed: the
+    reference's capture_cudagraph (model_runner.py:691-705) warms every bucket eagerly from the largest
+    batch downward and the split count is not monotone in the batch, so a later warm-up may need more
+    bytes than a graph captured before it -- that graph keeps replaying into the old pointer."""
+    old = _WS_CACHE.get(key)
+    if old is not None:
+        _WS_RETIRED.append(old)
+    # zeros: the head of the workspace holds the arrival tickets of the fused split merge, which every
+    # launch expects to find at zero and leaves at zero (include/b200attn.h, b200_attn_decode)
+    ws = torch.zeros(nbytes, dtype=torch.uint8, device=device)
+    _WS_CACHE[key] = ws
+    return ws
 
 
 def _workspace_for(batch: int, num_heads: int, splits: int, device) -> Optional[torch.Tensor]:
     if splits <= 1:
         return None
-    key = (device.index if device.index is not None else torch.cuda.current_device())
+    key = _device_key(device)
     ws = _WS_CACHE.get(key)
     need = load_library().b200_decode_workspace_bytes(batch, num_heads, splits)
     if ws is None or ws.numel() < need:
         if torch.cuda.is_current_stream_capturing():
             raise RuntimeError("b200attn: decode workspace must be sized before CUDA-graph capture "
                                "(call ops.reserve_decode_workspace first)")
-        ws = torch.empty(int(need * 1.25) + 256, dtype=torch.uint8, device=device)
-        _WS_CACHE[key] = ws
+        ws = _grow_workspace(key, int(need * 1.25) + 256, device)
     return ws
 
 
@@ -87,15 +94,14 @@ def reserve_decode_workspace(max_batch: int, num_heads: int, num_kv_heads: int, 
     """Size the per-device split-K workspace for the worst graph bucket (call before capture)."""
     lib = load_library()
     worst = 0
-    bs = 1
     cands = sorted({1, 2, 4, 8, *range(16, max_batch + 1, 16), max_batch})
     for bs in cands:
         s = lib.b200_decode_plan(bs, num_kv_heads, max_context)
         worst = max(worst, lib.b200_decode_workspace_bytes(bs, num_heads, s))
-    key = (torch.device(device).index if torch.device(device).index is not None else torch.cuda.current_device())
+    key = _device_key(device)
     cur = _WS_CACHE.get(key)
     if cur is None or cur.numel() < worst:
-        _WS_CACHE[key] = torch.empty(worst + 256, dtype=torch.uint8, device=device)
+        _grow_workspace(key, worst + 256, device)
 
 
 def attn_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, context_lens: torch.Tensor,
@@ -221,7 +227,10 @@ def attn_varlen_planned(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_se
     if out is None:
         out = torch.empty((T, Hq, D), dtype=q.dtype, device=q.device)
     lib = load_library()
-    if max_seqlen_q > 1:
+    # The prefill kernel runs whenever the plan may hold work for it: always for an unpaged call (its
+    # 1-token rows are NOT routed to decode -- a step of 1-token prompts without a prefix hit must still
+    # produce out = v, as flash_attn_varlen_func does), and for a paged call with any multi-token row.
+    if max_seqlen_q > 1 or not plan.route_decode:
         check(lib.b200_attn_prefill_planned(q.data_ptr(), q.stride(0), k.data_ptr(), v.data_ptr(), ks, vs,
                                             out.data_ptr(), out.stride(0), cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr(),
                                             bt_ptr, bt_stride, B, T, int(max_seqlen_q), int(max_seqlen_k), Hq, Hkv, D, PAGE,
@@ -360,8 +369,10 @@ class TpAllReduce:
         return ar_choose_form(self.world, nbytes, self.max_bytes, self.two_shot_min_bytes, self.two_shot_form)
 
     def fits(self, t: torch.Tensor) -> bool:
+        """Carrier choice depends on dtype, shape and layout only -- never on the address, which may differ
+        between ranks: a rank that went to NCCL alone would leave its peers spinning."""
         return (t.is_cuda and t.dtype == torch.bfloat16 and t.is_contiguous() and t.numel() % 8 == 0
-                and t.numel() * 2 <= self.max_bytes and t.data_ptr() % 16 == 0)
+                and t.numel() * 2 <= self.max_bytes)
 
     def all_reduce_(self, t: torch.Tensor, two_shot: Optional[bool] = None) -> torch.Tensor:
         if not self.fits(t):
@@ -369,9 +380,25 @@ class TpAllReduce:
                                f"numel % 8 == 0, <= {self.max_bytes} bytes)")
         if two_shot is None:
             two_shot = self.choose_form(t.numel() * 2)
-        check(self._lib.b200_allreduce_bf16(self._comm, t.data_ptr(), t.numel(), int(two_shot), _stream()),
+        work = t if t.data_ptr() % 16 == 0 else t.clone()        # a misaligned view is reduced through a copy
+        check(self._lib.b200_allreduce_bf16(self._comm, work.data_ptr(), work.numel(), int(two_shot), _stream()),
               "b200_allreduce_bf16")
+        if work is not t:
+            t.copy_(work)
         return t
+
+    def status(self) -> int:
+        """0 = healthy, 1 = a wait inside a launch timed out since creation.  Synchronises the device."""
+        import ctypes
+        out = ctypes.c_int32(0)
+        check(self._lib.b200_ar_status(self._comm, ctypes.byref(out)), "b200_ar_status")
+        return out.value
+
+    def destroy(self) -> None:
+        """Close the peers' IPC mappings and free the buffers (the caller synchronised device and group)."""
+        if self._comm is not None:
+            check(self._lib.b200_ar_destroy(self._comm), "b200_ar_destroy")
+            self._comm = None
 
 
 _TP_AR = None
@@ -416,3 +443,166 @@ def tp_all_reduce_(t: torch.Tensor) -> torch.Tensor:
         return _TP_AR.all_reduce_(t)
     dist.all_reduce(t)
     return t
+
+
+# ------------------------------------------------- (f3) all-reduce fused with add + RMSNorm on NVLS multicast
+class NvlsAllReduce:
+    """csrc/allreduce_nvls.cu: ONE launch per rank = all-reduce of the RowParallelLinear partial sums (in-switch
+    multimem.ld_reduce) + residual add + RMSNorm (linear.py:407-410 followed by layernorm.py:95-141).  The
+    symmetric buffer and its multicast mapping come from torch.distributed._symmetric_memory on the reference's
+    own process group (plumbing only: cuMemCreate / cuMulticast* and the handle exchange)."""
+
+    def __init__(self, group, max_bytes: int, device=None):
+        import ctypes
+        import torch.distributed as dist
+        lib = load_library()
+        self._lib = lib
+        self.world = dist.get_world_size(group) if group is not None else 1
+        self.rank = dist.get_rank(group) if group is not None else 0
+        self.max_bytes = int(max_bytes)
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        nbytes = lib.b200_nvls_buffer_bytes(self.max_bytes)
+        mc_ptr = None
+        if self.world > 1:
+            import torch.distributed._symmetric_memory as symm_mem
+            self.buf = symm_mem.empty(nbytes, dtype=torch.uint8, device=dev)
+            self.hdl = symm_mem.rendezvous(self.buf, group)
+            mc_ptr = int(self.hdl.multicast_ptr)
+            if not mc_ptr:
+                raise RuntimeError("b200attn: this group has no NVLS multicast mapping (multicast_ptr == 0)")
+        else:
+            self.buf = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        comm = ctypes.c_void_p()
+        check(lib.b200_nvls_create(self.rank, self.world, self.buf.data_ptr(), mc_ptr, self.max_bytes,
+                                   ctypes.byref(comm)), "b200_nvls_create")
+        self._comm = comm
+        self.one_shot_budget = int(__import__("os").environ.get("B200ATTN_NVLS_ONE_SHOT_BUDGET", 3 << 19))
+        if self.world > 1:
+            dist.barrier(group)            # every rank zeroed its flags before anyone can signal (b200attn.h)
+
+    def one_shot(self, nbytes: int) -> bool:
+        """Form policy, a pure function of (group size, message bytes): every rank reducing every row itself
+        moves (world - 2) x message more bytes over NVLink than reduce-scatter + multicast all-gather but saves
+        the second barrier (~5 us); at the measured 770 GB/s per direction that pays up to ~1.5 MB extra."""
+        return nbytes * max(self.world - 2, 0) <= self.one_shot_budget
+
+    def fits(self, x: torch.Tensor) -> bool:
+        return (x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 2 and x.is_contiguous()
+                and x.shape[1] % 8 == 0 and x.shape[1] <= 16384 and 0 < x.numel() * 2 <= self.max_bytes)
+
+    def all_reduce_add_rms_norm(self, x: torch.Tensor, residual: Optional[torch.Tensor], weight: Optional[torch.Tensor],
+                                eps: float, one_shot: Optional[bool] = None, out: Optional[torch.Tensor] = None):
+        """(normed, residual) like RMSNorm.forward(x_allreduced, residual); weight None => plain all-reduce -> out."""
+        if not self.fits(x):
+            raise RuntimeError("b200attn: tensor does not fit the NVLS fused all-reduce")
+        T, hidden = x.shape
+        if residual is not None:
+            _need_cuda_bf16(residual, "residual")
+            assert residual.is_contiguous() and residual.shape == x.shape
+        if weight is not None:
+            _need_cuda_bf16(weight, "weight")
+            assert weight.is_contiguous() and weight.numel() == hidden
+        if one_shot is None:
+            one_shot = self.one_shot(x.numel() * 2)
+        if out is None:
+            out = torch.empty_like(x)
+        xin = x if x.data_ptr() % 16 == 0 else x.clone()
+        check(self._lib.b200_nvls_allreduce_add_rmsnorm(
+            self._comm, xin.data_ptr(), residual.data_ptr() if residual is not None else None,
+            weight.data_ptr() if weight is not None else None, float(eps), out.data_ptr(), T, hidden,
+            1 if one_shot else 0, _stream()), "b200_nvls_allreduce_add_rmsnorm")
+        return out if residual is None else (out, residual)
+
+    def status(self) -> int:
+        import ctypes
+        out = ctypes.c_int32(0)
+        check(self._lib.b200_nvls_status(self._comm, ctypes.byref(out)), "b200_nvls_status")
+        return out.value
+
+    def destroy(self) -> None:
+        if self._comm is not None:
+            check(self._lib.b200_nvls_destroy(self._comm), "b200_nvls_destroy")
+            self._comm = None
+
+
+_TP_NVLS = None          # None = not tried yet, False = unavailable (multicast setup failed; the peer-store forms carry on)
+_DEFER_DEPTH = 0         # > 0 while a patched model forward is running: RowParallelLinear may hand over partial sums
+_PENDING = None          # partial sums of the last RowParallelLinear whose all-reduce has been deferred to its RMSNorm
+NVLS_DEFAULT_MAX_BYTES = 8 << 20
+
+
+def tp_nvls():
+    """The process-wide NVLS communicator of the tensor-parallel group, built on first use (every rank reaches the
+    first RowParallelLinear of the warm-up forward together, model_runner.py:311-316).  B200ATTN_NVLS=0, a group
+    without multicast support or a failed rendezvous leave the (already measured) peer-store all-reduce + separate
+    RMSNorm kernel in charge -- never a silent NCCL-only path for messages the peer-memory kernels can carry."""
+    import os
+    import torch.distributed as dist
+    global _TP_NVLS
+    if _TP_NVLS is None:
+        _TP_NVLS = False
+        if os.environ.get("B200ATTN_NVLS", "1") != "0" and dist.is_initialized() and 1 < dist.get_world_size() <= 8:
+            ok = 1
+            try:
+                comm = NvlsAllReduce(dist.group.WORLD, int(os.environ.get("B200ATTN_NVLS_MAX_BYTES", NVLS_DEFAULT_MAX_BYTES)))
+            except Exception as exc:                            # noqa: BLE001 -- any set-up failure means "unavailable"
+                comm, ok = None, 0
+                if dist.get_rank() == 0:
+                    print(f"b200attn: NVLS fused all-reduce unavailable ({type(exc).__name__}: {exc}); "
+                          "using the peer-store all-reduce + RMSNorm kernels", flush=True)
+            # all ranks must agree, or some would defer their all-reduce and others not
+            flag = torch.tensor([ok], device="cuda", dtype=torch.int32)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            if int(flag.item()) == 1:
+                _TP_NVLS = comm
+    return _TP_NVLS
+
+
+class deferred_all_reduce:
+    """Context manager around a model forward: inside it `tp_row_parallel_output` may return UN-reduced partial
+    sums and remember them; the RMSNorm that consumes them (`tp_norm_input`) runs the fused kernel.  Anything
+    still pending at exit is reduced in place, so no caller ever sees partial sums outside."""
+
+    def __enter__(self):
+        global _DEFER_DEPTH
+        _DEFER_DEPTH += 1
+        return self
+
+    def __exit__(self, *exc):
+        global _DEFER_DEPTH
+        _DEFER_DEPTH -= 1
+        if _DEFER_DEPTH == 0:
+            flush_pending_all_reduce()
+        return False
+
+
+def flush_pending_all_reduce() -> None:
+    global _PENDING
+    if _PENDING is not None:
+        t, _PENDING = _PENDING, None
+        tp_all_reduce_(t)
+
+
+def tp_row_parallel_output(y: torch.Tensor) -> torch.Tensor:
+    """RowParallelLinear's `dist.all_reduce(y)` (linear.py:410): immediately, or -- inside `deferred_all_reduce`,
+    for messages the NVLS kernel carries -- left to the RMSNorm that follows (qwen3.py:370,374,440)."""
+    global _PENDING
+    flush_pending_all_reduce()                                  # an earlier deferred sum nobody normalised
+    if _DEFER_DEPTH > 0:
+        nv = tp_nvls()
+        if nv and nv.fits(y):
+            _PENDING = y
+            return y
+    return tp_all_reduce_(y)
+
+
+def tp_add_rms_norm(x: torch.Tensor, residual: Optional[torch.Tensor], weight: torch.Tensor, eps: float):
+    """RMSNorm.forward(x, residual) (layernorm.py:143-165); when `x` is the pending partial-sum tensor the
+    all-reduce happens inside the same launch."""
+    global _PENDING
+    if _PENDING is not None:
+        if _PENDING is x and residual is not None:
+            _PENDING = None
+            return _TP_NVLS.all_reduce_add_rms_norm(x, residual, weight, eps)
+        flush_pending_all_reduce()
+    return rms_norm(x, weight, eps, residual)

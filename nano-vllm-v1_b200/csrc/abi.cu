@@ -9,16 +9,41 @@
 #include "launch.h"
 
 namespace b200 {
+int current_device() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { (void)cudaGetLastError(); return -1; }
+    return dev;
+}
+
 int sm_count() {
-    static int cached = 0;
-    if (cached == 0) {
-        int dev = 0, n = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess ||
-            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
-            n = 148;                                              // B200
-        cached = n;
+    static int cached[64] = {0};                                  // per device: a process may touch several GPUs
+    const int dev = current_device();
+    if (dev >= 0 && dev < 64 && cached[dev] > 0) return cached[dev];
+    int n = 0;
+    if (dev < 0 || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+        n = 148;                                                  // B200
+    if (dev >= 0 && dev < 64) cached[dev] = n;
+    return n;
+}
+
+// B200ATTN_DECODE_FUSED_REDUCE=0 restores the separate decode_reduce_kernel launch (A/B knob).
+static bool decode_fused_reduce() {
+    static int v = -1;
+    if (v < 0) {
+        const char* env = getenv("B200ATTN_DECODE_FUSED_REDUCE");
+        v = (env && env[0] == '0') ? 0 : 1;
     }
-    return cached;
+    return v == 1;
+}
+
+// Carve the caller's split-K workspace: [ tickets (DEC_TICKET_BYTES, zero) | partial O fp32 | LSE fp32 ].
+static void carve_decode_workspace(DecodeArgs& a, void* workspace) {
+    a.ws_o = nullptr; a.ws_lse = nullptr; a.tickets = nullptr;
+    if (!workspace) return;
+    a.ws_o = (float*)((char*)workspace + DEC_TICKET_BYTES);
+    a.ws_lse = a.ws_o + (size_t)a.batch * a.num_splits * a.Hq * B200_HD_CONST;
+    if (decode_fused_reduce() && (size_t)a.batch * a.Hkv * sizeof(int32_t) <= DEC_TICKET_BYTES)
+        a.tickets = (int32_t*)workspace;
 }
 }  // namespace b200
 
@@ -89,7 +114,7 @@ int b200_decode_plan(int32_t batch, int32_t num_kv_heads, int32_t max_context_le
 
 size_t b200_decode_workspace_bytes(int32_t batch, int32_t num_heads, int32_t num_splits) {
     if (num_splits <= 1 || batch <= 0 || num_heads <= 0) return 0;
-    return (size_t)batch * num_splits * num_heads * (B200_HD_CONST + 1) * sizeof(float);
+    return DEC_TICKET_BYTES + (size_t)batch * num_splits * num_heads * (B200_HD_CONST + 1) * sizeof(float);
 }
 
 int b200_attn_decode(const void* q, int64_t q_token_stride, const void* k_cache, const void* v_cache,
@@ -113,8 +138,7 @@ int b200_attn_decode(const void* q, int64_t q_token_stride, const void* k_cache,
     a.out = out; a.out_token_stride = out_token_stride; a.context_lens = context_lens;
     a.block_tables = block_tables; a.bt_row_stride = bt_row_stride;
     a.batch = batch; a.Hq = num_heads; a.Hkv = num_kv_heads; a.scale = softmax_scale; a.num_splits = num_splits;
-    a.ws_o = (float*)workspace;
-    a.ws_lse = workspace ? (float*)workspace + (size_t)batch * num_splits * num_heads * B200_HD_CONST : nullptr;
+    carve_decode_workspace(a, workspace);
     return launch_attn_decode(a, (cudaStream_t)stream);
 }
 
@@ -229,8 +253,7 @@ int b200_attn_decode_varlen(const void* q, int64_t q_token_stride, const void* k
     a.out = out; a.out_token_stride = out_token_stride; a.context_lens = nullptr;
     a.block_tables = block_tables; a.bt_row_stride = bt_row_stride;
     a.batch = batch; a.Hq = num_heads; a.Hkv = num_kv_heads; a.scale = softmax_scale; a.num_splits = num_splits;
-    a.ws_o = (float*)workspace;
-    a.ws_lse = workspace ? (float*)workspace + (size_t)batch * num_splits * num_heads * B200_HD_CONST : nullptr;
+    carve_decode_workspace(a, workspace);
     const int32_t* pl = (const int32_t*)plan;
     a.cu_q = cu_seqlens_q; a.cu_k = cu_seqlens_k;
     a.n_rows = pl + 1;
@@ -245,6 +268,7 @@ int b200_qk_norm_rope(const void* q, int64_t q_token_stride, const void* k, int6
     if (num_tokens < 0 || num_heads <= 0 || num_kv_heads <= 0) return B200_ERR_RANGE;
     if (num_tokens == 0) return B200_OK;
     if (!q || !k || !positions || !cos_sin_cache || !q_out || !k_out) return B200_ERR_NULL;   /* NULL weights => rotation only */
+    if ((q_weight == nullptr) != (k_weight == nullptr)) return B200_ERR_NULL;                 /* both or neither */
     if (head_dim != B200_HD_CONST) return B200_ERR_SHAPE;
     if (!aligned16(q) || !aligned16(k) || !aligned16(q_out) || !aligned16(k_out) || !stride_ok(q_token_stride) ||
         !stride_ok(k_token_stride) || (reinterpret_cast<uintptr_t>(cos_sin_cache) & 15))
@@ -263,6 +287,7 @@ int b200_qk_norm_rope_store(const void* q, int64_t q_token_stride, const void* k
     if (num_tokens == 0) return B200_OK;
     if (!q || !k || !v || !positions || !cos_sin_cache || !q_out || !k_cache || !v_cache || !slot_mapping)
         return B200_ERR_NULL;                                       /* k_out and the weights may be NULL */
+    if ((q_weight == nullptr) != (k_weight == nullptr)) return B200_ERR_NULL;   /* both weights or neither */
     if (head_dim != B200_HD_CONST) return B200_ERR_SHAPE;
     if (!aligned16(q) || !aligned16(k) || !aligned16(v) || !aligned16(q_out) || (k_out && !aligned16(k_out)) ||
         !aligned16(k_cache) || !aligned16(v_cache) || !stride_ok(q_token_stride) || !stride_ok(k_token_stride) ||

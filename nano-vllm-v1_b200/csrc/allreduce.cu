@@ -37,7 +37,15 @@ struct ArComm {
     int32_t rank, world;
     size_t slot_bytes;
     uint32_t* epoch;                            // device: [0] = completed all-reduces, [1] = blocks done in this launch,
-                                                // [2],[3] = arrive counter / go flag of barrier A, [4],[5] = of barrier B
+                                                // [2],[3] = arrive counter / go flag of barrier A, [4],[5] = of barrier B,
+                                                // [7] = sticky error (a bounded wait timed out)
+    uint64_t timeout_ns;                        // bound of every wait (B200ATTN_AR_TIMEOUT_S, default 30 s)
+};
+
+// Host-side handle behind the opaque `comm` pointer of the C ABI.
+struct ArHandle {
+    ArComm dev;                                 // passed to the kernels by value
+    int32_t max_blocks;                         // co-resident blocks on this device (<= AR_BLOCKS): all blocks spin on each other
 };
 
 // The flag itself travels with relaxed system-scope accesses; ordering comes from ONE system fence before
@@ -65,6 +73,22 @@ __device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
 // and one per block (48 blocks: +9 us measured) serialises; so the blocks of a rank first meet on a local
 // counter (gpu scope), block 0 alone talks to the peers (two system fences per barrier per rank), then
 // releases its siblings through a local flag.  `which` = 0 / 1 selects flag set A / B.
+// Bounded wait helper: polls `done()`; after c.timeout_ns of wall clock it raises the communicator's sticky error
+// word (epoch[7], read by b200_ar_status) and gives up, so a stalled or dead peer costs a wrong result that the
+// host can detect -- not a trapped, unusable CUDA context.
+template <typename F>
+__device__ __forceinline__ void ar_spin(const ArComm& c, F done) {
+    uint64_t t0 = 0;
+    for (uint32_t spins = 0; !done(); ++spins) {
+        if ((spins & 1023u) == 1023u) {
+            uint64_t now;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > c.timeout_ns) { atomicExch(c.epoch + 7, 1u); return; }
+        }
+    }
+}
+
 __device__ __forceinline__ void ar_barrier(const ArComm& c, int which, size_t flags_off, uint32_t epoch) {
     uint32_t* arrive = c.epoch + 2 + 2 * which;
     uint32_t* go = arrive + 1;
@@ -75,20 +99,17 @@ __device__ __forceinline__ void ar_barrier(const ArComm& c, int which, size_t fl
     }
     if (blockIdx.x == 0) {
         if (threadIdx.x < 32) {
-            uint32_t spins = 0;
             if (threadIdx.x == 0) {
-                while (ld_acquire_gpu(arrive) < gridDim.x)
-                    if (++spins > (1u << 27)) __trap();
-                __threadfence_system();         // everything this rank wrote is visible before the flags are
+                ar_spin(c, [&] { return ld_acquire_gpu(arrive) >= gridDim.x; });
+                __threadfence_system();         // everything this rank wrote is visible before the flags are:
+                for (int r = 0; r < c.world; ++r)   // the SAME thread fences and stores (release pattern)
+                    st_relaxed_sys(reinterpret_cast<uint32_t*>(c.peer[r] + flags_off) + c.rank, epoch);
             }
             __syncwarp();
             if ((int)threadIdx.x < c.world) {
-                uint32_t* theirs = reinterpret_cast<uint32_t*>(c.peer[threadIdx.x] + flags_off) + c.rank;
-                st_relaxed_sys(theirs, epoch);
                 const uint32_t* mine = reinterpret_cast<const uint32_t*>(c.peer[c.rank] + flags_off) + threadIdx.x;
-                spins = 0;
-                while ((int32_t)(ld_relaxed_sys(mine) - epoch) < 0)
-                    if (++spins > (1u << 27)) __trap();
+                ar_spin(c, [&] { return (int32_t)(ld_relaxed_sys(mine) - epoch) >= 0; });
+                __threadfence_system();         // acquire side, in the lane that observed the flag
             }
             __syncwarp();
             if (threadIdx.x == 0) {
@@ -97,11 +118,7 @@ __device__ __forceinline__ void ar_barrier(const ArComm& c, int which, size_t fl
             }
         }
     }
-    if (threadIdx.x == 0) {
-        uint32_t spins = 0;
-        while ((int32_t)(ld_acquire_gpu(go) - epoch) < 0)
-            if (++spins > (1u << 27)) __trap();
-    }
+    if (threadIdx.x == 0) ar_spin(c, [&] { return (int32_t)(ld_acquire_gpu(go) - epoch) >= 0; });
     __syncthreads();
 }
 
@@ -289,6 +306,13 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_push1_kernel(const ArCom
     }
 }
 
+uint64_t ar_timeout_ns() {
+    const char* env = getenv("B200ATTN_AR_TIMEOUT_S");
+    double sec = env ? atof(env) : 30.0;
+    if (!(sec > 0.0)) sec = 30.0;
+    return (uint64_t)(sec * 1e9);
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -328,44 +352,91 @@ int b200_ar_open(const void* ipc_handle64, void** peer_ptr) {
 int b200_ar_create(int rank, int world, void* const* peer_ptrs, size_t max_msg_bytes, void** comm_out) {
     if (!peer_ptrs || !comm_out) return B200_ERR_NULL;
     if (world < 1 || world > AR_MAX_WORLD || rank < 0 || rank >= world) return B200_ERR_RANGE;
-    ArComm* c = new ArComm();
+    ArHandle* h = new ArHandle();
+    ArComm* c = &h->dev;
     for (int r = 0; r < AR_MAX_WORLD; ++r) c->peer[r] = r < world ? (uint8_t*)peer_ptrs[r] : nullptr;
     c->rank = rank; c->world = world;
     c->slot_bytes = 2 * ((max_msg_bytes + 1023) / 1024 * 1024);
+    c->timeout_ns = ar_timeout_ns();
     cudaError_t e = cudaMalloc((void**)&c->epoch, 8 * sizeof(uint32_t));
     if (e == cudaSuccess) e = cudaMemset(c->epoch, 0, 8 * sizeof(uint32_t));
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
-    if (e != cudaSuccess) { delete c; return (int)e; }
-    *comm_out = c;
+    // co-residency bound: the smallest occupancy of the four kernels x SM count
+    int per_sm = 1 << 30;
+    if (e == cudaSuccess) {
+        const void* ks[4] = {(const void*)allreduce_kernel<false>, (const void*)allreduce_kernel<true>,
+                             (const void*)allreduce_push_kernel, (const void*)allreduce_push1_kernel};
+        for (int i = 0; i < 4 && e == cudaSuccess; ++i) {
+            int n = 0;
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, ks[i], AR_THREADS, 0);
+            if (n < per_sm) per_sm = n;
+        }
+    }
+    if (e != cudaSuccess) { if (c->epoch) cudaFree(c->epoch); delete h; return (int)e; }
+    int64_t cap = (int64_t)per_sm * sm_count();
+    h->max_blocks = (int32_t)(cap < 1 ? 1 : (cap > AR_BLOCKS ? AR_BLOCKS : cap));
+    *comm_out = h;
+    return B200_OK;
+}
+
+// Tear-down (the reference destroys its process group at exit, model_runner.py:187-193): closes the IPC
+// mappings of the peers' buffers, frees the local buffer (it must come from b200_ar_alloc) and the
+// communicator.  The caller synchronises the device and the group first (no rank may still be inside a call).
+int b200_ar_destroy(void* comm) {
+    if (!comm) return B200_ERR_NULL;
+    ArHandle* h = (ArHandle*)comm;
+    ArComm* c = &h->dev;
+    int rc = B200_OK;
+    for (int r = 0; r < c->world; ++r) {
+        if (!c->peer[r]) continue;
+        cudaError_t e = (r == c->rank) ? cudaFree(c->peer[r]) : cudaIpcCloseMemHandle(c->peer[r]);
+        if (e != cudaSuccess && rc == B200_OK) rc = (int)e;
+    }
+    if (c->epoch) { cudaError_t e = cudaFree(c->epoch); if (e != cudaSuccess && rc == B200_OK) rc = (int)e; }
+    delete h;
+    return rc;
+}
+
+// 0 = healthy; 1 = some wait inside a kernel exceeded B200ATTN_AR_TIMEOUT_S since the communicator was made
+// (results after that point are not trustworthy).  Synchronises the device: for tests, tools and shutdown.
+int b200_ar_status(void* comm, int32_t* status_out) {
+    if (!comm || !status_out) return B200_ERR_NULL;
+    const ArComm* c = &((const ArHandle*)comm)->dev;
+    uint32_t v = 0;
+    cudaError_t e = cudaMemcpy(&v, c->epoch + 7, sizeof(v), cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) return (int)e;
+    *status_out = (int32_t)v;
     return B200_OK;
 }
 
 int b200_allreduce_bf16(void* comm, void* data, int64_t n_elems, int two_shot, void* stream) {
     if (!comm || !data) return B200_ERR_NULL;
-    const ArComm* c = (const ArComm*)comm;
+    const ArHandle* h = (const ArHandle*)comm;
+    const ArComm* c = &h->dev;
     if (n_elems < 0 || (n_elems & 7) || (size_t)n_elems * 2 > c->slot_bytes / 2) return B200_ERR_RANGE;
     if (((uintptr_t)data & 15) != 0) return B200_ERR_ALIGN;
     if (n_elems == 0) return B200_OK;
     // About four 16-byte chunks per thread in the phase that reads the peers (memory-level parallelism comes
     // from the unrolled loads, not from long loops); the grid depends only on n_elems and the group size, so it
-    // is the same on every rank.  All blocks spin on each other, so the grid must stay co-resident (<= 128 < 148 SMs).
+    // is the same on every rank.  All blocks spin on each other: the grid is capped at the co-resident count and
+    // launched cooperatively.
     const bool two = (two_shot == 1 || two_shot == 2) && c->world > 2;
     // push form: world x ceil(n16 / world) chunks of contributions must stay inside the first half of a slot
     // (only the largest message with a group size that does not divide it can miss by world - 1 chunks)
     if (two && two_shot == 2 && (size_t)((n_elems / 8 + c->world - 1) / c->world) * c->world * 16 > c->slot_bytes / 2) two_shot = 1;
     const int64_t work = two ? (n_elems / 8 + c->world - 1) / c->world : (n_elems / 8 + 3) / 4;   // chunks per thread-step
     int64_t grid = (work + AR_THREADS - 1) / AR_THREADS;
-    grid = grid < 1 ? 1 : (grid > AR_BLOCKS ? AR_BLOCKS : grid);
+    grid = grid < 1 ? 1 : (grid > h->max_blocks ? h->max_blocks : grid);
+    cudaStream_t st = (cudaStream_t)stream;
+    uint4* d = (uint4*)data;
+    const int64_t n16 = n_elems / 8;
     if (two_shot == 3) {
         if ((size_t)n_elems * 2 * c->world > c->slot_bytes) return B200_ERR_RANGE;
-        allreduce_push1_kernel<<<(int)grid, AR_THREADS, 0, (cudaStream_t)stream>>>(*c, (uint4*)data, n_elems / 8);
-    } else if (two && two_shot == 2)
-        allreduce_push_kernel<<<(int)grid, AR_THREADS, 0, (cudaStream_t)stream>>>(*c, (uint4*)data, n_elems / 8);
-    else if (two)
-        allreduce_kernel<true><<<(int)grid, AR_THREADS, 0, (cudaStream_t)stream>>>(*c, (uint4*)data, n_elems / 8);
-    else
-        allreduce_kernel<false><<<(int)grid, AR_THREADS, 0, (cudaStream_t)stream>>>(*c, (uint4*)data, n_elems / 8);
-    return (int)cudaGetLastError();
+        return launch_coop(allreduce_push1_kernel, (int)grid, AR_THREADS, st, *c, d, n16);
+    }
+    if (two && two_shot == 2) return launch_coop(allreduce_push_kernel, (int)grid, AR_THREADS, st, *c, d, n16);
+    if (two) return launch_coop(allreduce_kernel<true>, (int)grid, AR_THREADS, st, *c, d, n16);
+    return launch_coop(allreduce_kernel<false>, (int)grid, AR_THREADS, st, *c, d, n16);
 }
 
 }  // extern "C"

@@ -46,6 +46,7 @@ struct DecodeParams {
     const int32_t* context_lens; const int32_t* block_tables; int32_t bt_row_stride;
     int32_t Hq, Hkv, G; float scale_log2; int32_t num_splits;
     float* ws_o; float* ws_lse;
+    int32_t* tickets;       // non-null: the last split of a (row, kv head) to arrive merges (no reduce launch)
     // varlen form (mixed batches): rows come from a device-built list, lengths from cu_seqlens
     const int32_t* cu_q; const int32_t* cu_k; const int32_t* row_list; const int32_t* n_rows;
 };
@@ -87,13 +88,17 @@ __global__ void __launch_bounds__(DEC_WARPS * 32, MIN_CTAS) paged_decode_kernel(
     const int per = (chunks_total + n_eff - 1) / n_eff;
     const int c_begin = s * per;
     const int c_end = min(chunks_total, c_begin + per);
+    // splits of this row that hold tokens; the fused merge counts exactly these arrivals
+    const int n_part = per > 0 ? (chunks_total + per - 1) / per : 0;
+    const bool fused = p.tickets != nullptr;
+    const bool direct = S == 1 || (fused && n_part == 1);       // this CTA alone owns the row: write `out` itself
 
     if (c_begin >= c_end) {                                   // empty split or padding row (len 0)
-        if (S == 1) {
+        if (S == 1 || (fused && s == 0)) {                    // (fused: s == 0 is empty only when the row is)
             for (int r = 0; r < G; ++r)
                 for (int t = threadIdx.x; t < B200_HD; t += DEC_THREADS)
                     p.out[tok * p.out_token_stride + (int64_t)(h * G + r) * B200_HD + t] = __float2bfloat16(0.f);
-        } else if (threadIdx.x < G) {
+        } else if (!fused && threadIdx.x < G) {
             p.ws_lse[((int64_t)bi * S + s) * p.Hq + h * G + threadIdx.x] = -INFINITY;
         }
         return;
@@ -255,13 +260,41 @@ __global__ void __launch_bounds__(DEC_WARPS * 32, MIN_CTAS) paged_decode_kernel(
         }
         const float val = acc / den;
         const int head = h * G + r;
-        if (S == 1) {
+        if (direct) {
             p.out[tok * p.out_token_stride + (int64_t)head * B200_HD + t] = __float2bfloat16_rn(val);
         } else {
             const int64_t widx = ((int64_t)bi * S + s) * p.Hq + head;
             p.ws_o[widx * B200_HD + t] = val;
             if (t == 0) p.ws_lse[widx] = ms + log2f(den);
         }
+    }
+    if (direct || !fused) return;
+
+    // ---- fused split merge: the last of this (row, kv head)'s n_part CTAs to arrive reduces them all ----
+    volatile int* s_last = reinterpret_cast<volatile int*>(smem);   // the warp-merge scratch is dead after the barrier
+    __threadfence();                                          // this thread's partials before the ticket
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int32_t* ticket = p.tickets + (int64_t)bi * p.Hkv + h;
+        const int t = atomicAdd(ticket, 1);
+        *s_last = (t == n_part - 1);
+        if (t == n_part - 1) *ticket = 0;                     // self re-arming: every launch finds zeros (graph replay)
+        __threadfence();
+    }
+    __syncthreads();
+    if (!*s_last) return;
+    for (int idx = threadIdx.x; idx < G * B200_HD; idx += DEC_THREADS) {
+        const int head = h * G + (idx >> 7), t = idx & (B200_HD - 1);
+        const float* lse = p.ws_lse + ((int64_t)bi * S) * p.Hq + head;
+        float mx = -INFINITY;
+        for (int ss = 0; ss < n_part; ++ss) mx = fmaxf(mx, __ldcg(lse + (int64_t)ss * p.Hq));
+        float acc = 0.f, den = 0.f;
+        for (int ss = 0; ss < n_part; ++ss) {
+            const float w = fast_exp2(__ldcg(lse + (int64_t)ss * p.Hq) - mx);
+            acc += w * __ldcg(p.ws_o + (((int64_t)bi * S + ss) * p.Hq + head) * B200_HD + t);
+            den += w;
+        }
+        p.out[tok * p.out_token_stride + (int64_t)head * B200_HD + t] = __float2bfloat16_rn(acc / den);
     }
 }
 
@@ -291,12 +324,12 @@ __global__ void __launch_bounds__(B200_HD) decode_reduce_kernel(const DecodePara
 
 template <int W, int ST, int MC>
 static int launch_decode_shape(const DecodeParams& p, int64_t grid, cudaStream_t stream) {
-    static bool attr_set = false;
+    static PerDeviceOnce once;                                 // the opt-in is per device, not per process
     constexpr int SMEM = dec_smem_bytes(W, ST);
-    if (!attr_set) {
+    if (once.need()) {
         cudaError_t e = cudaFuncSetAttribute(paged_decode_kernel<W, ST, MC>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
         if (e != cudaSuccess) return (int)e;
-        attr_set = true;
+        once.done();
     }
     paged_decode_kernel<W, ST, MC><<<(unsigned)grid, W * 32, SMEM, stream>>>(p);
     return (int)cudaGetLastError();
@@ -329,6 +362,7 @@ int launch_attn_decode(const DecodeArgs& a, cudaStream_t stream) {
     p.Hq = a.Hq; p.Hkv = a.Hkv; p.G = a.Hq / a.Hkv;
     p.scale_log2 = a.scale * 1.4426950408889634f;
     p.num_splits = a.num_splits; p.ws_o = a.ws_o; p.ws_lse = a.ws_lse;
+    p.tickets = a.num_splits > 1 ? a.tickets : nullptr;
     p.cu_q = a.cu_q; p.cu_k = a.cu_k; p.row_list = a.row_list; p.n_rows = a.n_rows;
     if (a.batch == 0) return 0;
     const int64_t grid = (int64_t)a.batch * a.Hkv * a.num_splits;
@@ -341,7 +375,7 @@ int launch_attn_decode(const DecodeArgs& a, cudaStream_t stream) {
     }
     if (rc != 0) return rc;
     cudaError_t e = cudaSuccess;
-    if (a.num_splits > 1) {
+    if (a.num_splits > 1 && p.tickets == nullptr) {           // legacy two-launch form (B200ATTN_DECODE_FUSED_REDUCE=0)
         decode_reduce_kernel<<<(unsigned)(a.batch * a.Hq), B200_HD, 0, stream>>>(p, a.batch);
         e = cudaGetLastError();
     }

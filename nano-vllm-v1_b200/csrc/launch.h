@@ -4,12 +4,23 @@
 #include <cuda_runtime.h>
 #include <stddef.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #define B200_HD_CONST 128
 
 namespace b200 {
 
-int sm_count();
+int sm_count();                          // of the CURRENT device (cached per device)
+int current_device();
+
+// One-time per-device setup guard (cudaFuncSetAttribute opt-ins are per device; a process may touch
+// several GPUs, e.g. tests on cuda:1).
+struct PerDeviceOnce {
+    uint64_t mask = 0;
+    int dev = 0;
+    bool need() { dev = current_device(); return dev < 0 || dev >= 64 || !(mask >> dev & 1ull); }
+    void done() { if (dev >= 0 && dev < 64) mask |= 1ull << dev; }
+};
 
 int launch_kv_scatter(const void* key, const void* value, int64_t key_row_stride, int64_t value_row_stride,
                       void* k_cache, void* v_cache, const int32_t* slot_mapping,
@@ -36,11 +47,15 @@ struct DecodeArgs {
     const int32_t* context_lens; const int32_t* block_tables; int32_t bt_row_stride;
     int32_t batch, Hq, Hkv; float scale; int32_t num_splits;
     float* ws_o; float* ws_lse;
+    int32_t* tickets = nullptr;           // zeroed int32[batch * Hkv]: fused split merge (NULL => separate reduce launch)
     // varlen form: non-null => rows are row_list[0 .. *n_rows), lengths/tokens from cu_k / cu_q
     const int32_t* cu_q = nullptr; const int32_t* cu_k = nullptr;
     const int32_t* row_list = nullptr; const int32_t* n_rows = nullptr;
 };
 int launch_attn_decode(const DecodeArgs& a, cudaStream_t stream);
+// Fixed ticket region at the head of the split-K workspace (one int32 per (row, kv head)); must be zero
+// before the first launch, every launch leaves it zero.
+constexpr size_t DEC_TICKET_BYTES = 64 * 1024;
 
 struct PrefillArgs {
     const void* q; int64_t q_token_stride;
@@ -69,5 +84,23 @@ inline size_t plan_bytes(int32_t batch, int32_t total_q) {
 int launch_attn_plan(const int32_t* cu_q, const int32_t* cu_k, int32_t batch, int32_t route_decode, int32_t tile_rows,
                      int32_t* plan, int32_t max_items, cudaStream_t stream);
 int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32_t max_items, cudaStream_t stream);
+
+
+// ---- peer-memory collectives (allreduce.cu, allreduce_nvls.cu) ----------------------------------
+// Launch with the cooperative attribute: the driver either places ALL blocks at once or fails the launch, so
+// the blocks that spin on each other are co-resident whatever else is running on the device (another stream's
+// kernel holding SMs can delay the launch, never deadlock it).  Capturable in CUDA graphs.
+template <typename... KArgs, typename... Args>
+inline int launch_coop(void (*kernel)(KArgs...), int grid, int threads, cudaStream_t stream, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3((unsigned)threads); cfg.dynamicSmemBytes = 0; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    return (int)cudaLaunchKernelEx(&cfg, kernel, args...);
+}
+
+uint64_t ar_timeout_ns();   // B200ATTN_AR_TIMEOUT_S (default 30 s) in ns
 
 }  // namespace b200

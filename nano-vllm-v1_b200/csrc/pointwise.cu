@@ -7,26 +7,49 @@
 namespace b200 {
 
 // ------------------------------------------------------------------------------------------
-// (1) KV scatter.  One thread moves one 16-byte chunk of K and the matching chunk of V.
-//     Consecutive threads walk consecutive chunks of one token row => every warp issues
-//     full 512-byte coalesced loads and stores.  Reference: attention.py:74-90.
+// (1) KV scatter.  One thread moves SC_UNROLL 16-byte chunks of K and the matching chunks of V per
+//     step: all slot lookups, then all 2 x SC_UNROLL loads, then the stores -- 128 bytes in flight per
+//     thread, so a short launch (T x 4 x Hkv x 256 B: 134 MB at T = 16384, 8 kv heads) is not bound by
+//     the slot -> load -> store latency chain of one chunk.  Consecutive threads walk consecutive
+//     chunks of one token row => every warp issues full 512-byte coalesced loads and stores.
+//     POW2 = chunks per row is a power of two (1/2/4/8 kv heads); else a 32-bit divide (5 heads).
+//     Reference: attention.py:74-90.
 // ------------------------------------------------------------------------------------------
+constexpr int SC_UNROLL = 4;
+
+template <bool POW2>
 __global__ void __launch_bounds__(256) kv_scatter_kernel(
     const uint8_t* __restrict__ key, const uint8_t* __restrict__ value,
     int64_t key_row_bytes, int64_t value_row_bytes,
     uint8_t* __restrict__ k_cache, uint8_t* __restrict__ v_cache,
-    const int32_t* __restrict__ slot_mapping, int64_t total_chunks, int32_t chunks_per_row_log2) {
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_chunks; i += stride) {
-        const int64_t tok = i >> chunks_per_row_log2;
-        const int64_t c = i & ((1 << chunks_per_row_log2) - 1);
-        const int32_t slot = __ldg(slot_mapping + tok);
-        if (slot < 0) continue;                                           // attention.py:79-80
-        const int4 kv = ld_nc_v4(key + tok * key_row_bytes + c * 16);
-        const int4 vv = ld_nc_v4(value + tok * value_row_bytes + c * 16);
-        const int64_t dst = (((int64_t)slot) << (chunks_per_row_log2 + 4)) + c * 16;   // 64-bit: SURVEY 7.3(9)
-        st_v4(k_cache + dst, kv);
-        st_v4(v_cache + dst, vv);
+    const int32_t* __restrict__ slot_mapping, uint32_t total_chunks, uint32_t chunks_per_row, uint32_t lg) {
+    const uint32_t step = gridDim.x * (256u * SC_UNROLL);
+    for (uint32_t base = blockIdx.x * (256u * SC_UNROLL) + threadIdx.x; base < total_chunks; base += step) {
+        int4 kv[SC_UNROLL], vv[SC_UNROLL];
+        int64_t dst[SC_UNROLL];
+        bool ok[SC_UNROLL];
+#pragma unroll
+        for (int u = 0; u < SC_UNROLL; ++u) {
+            const uint32_t i = base + u * 256u;
+            ok[u] = false;
+            if (i < total_chunks) {
+                const uint32_t tok = POW2 ? i >> lg : i / chunks_per_row;
+                const uint32_t c = POW2 ? i & (chunks_per_row - 1) : i - tok * chunks_per_row;
+                const int32_t slot = __ldg(slot_mapping + tok);
+                if (slot >= 0) {                                              // attention.py:79-80
+                    ok[u] = true;
+                    kv[u] = ld_nc_v4(key + (int64_t)tok * key_row_bytes + c * 16);
+                    vv[u] = ld_nc_v4(value + (int64_t)tok * value_row_bytes + c * 16);
+                    dst[u] = ((int64_t)slot * chunks_per_row + c) * 16;       // 64-bit: SURVEY 7.3(9)
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < SC_UNROLL; ++u)
+            if (ok[u]) {
+                st_v4(k_cache + dst[u], kv[u]);
+                st_v4(v_cache + dst[u], vv[u]);
+            }
     }
 }
 
@@ -35,6 +58,9 @@ __global__ void __launch_bounds__(256) kv_scatter_kernel(
 //      Lane l owns elements [8l, 8l+8) of the low half and [64+8l, 64+8l+8) of the high half,
 //      i.e. both members of eight NeoX rotation pairs => two 16-byte loads + two 16-byte stores
 //      per lane, no cross-lane traffic for the rotation, a 3-step butterfly for the sum of squares.
+//      A thread works on NR_ROWS rows per step (grid-stride): every load of every row -- data, position,
+//      slot -- is issued before the first row is normalised, so 64 bytes of row data plus the dependent
+//      position -> cos/sin chain are in flight per thread.
 //      Roundings follow layernorm.py:85-93 and rotary_embedding.py:60-65 exactly:
 //      bf16(x*rstd), bf16(.*w), fp32 rotate (un-fused mul/sub), bf16.
 // ------------------------------------------------------------------------------------------
@@ -46,6 +72,8 @@ struct KvStoreArgs {
     __nv_bfloat16* k_cache; __nv_bfloat16* v_cache; const int32_t* slot_mapping;
 };
 
+constexpr int NR_ROWS = 2;
+
 template <bool STORE>
 __global__ void __launch_bounds__(256) qk_norm_rope_kernel(
     const __nv_bfloat16* __restrict__ q, int64_t q_token_stride,
@@ -53,96 +81,115 @@ __global__ void __launch_bounds__(256) qk_norm_rope_kernel(
     const int64_t* __restrict__ positions, const float* __restrict__ cos_sin,
     const __nv_bfloat16* __restrict__ q_weight, const __nv_bfloat16* __restrict__ k_weight, float eps,
     __nv_bfloat16* __restrict__ q_out, __nv_bfloat16* __restrict__ k_out,
-    int64_t total_rows, int32_t Hq, int32_t Hkv, const KvStoreArgs st) {
+    uint32_t total_rows, uint32_t Hq, uint32_t Hkv, const KvStoreArgs st) {
     const int sub = threadIdx.x & 7;
-    const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
-    const bool live = row < total_rows;                        // dead lanes still take part in the shuffles
-    const int32_t H = STORE ? Hq + 2 * Hkv : Hq + Hkv;
-    const int64_t tok = live ? row / H : 0;
-    const int32_t h = live ? (int32_t)(row - tok * H) : 0;
-    const bool is_q = h < Hq;
-    const bool is_v = STORE && h >= Hq + Hkv;
-    const __nv_bfloat16* src = is_q ? q + tok * q_token_stride + (int64_t)h * B200_HD
-                             : is_v ? st.v + tok * st.v_token_stride + (int64_t)(h - Hq - Hkv) * B200_HD
-                                    : k + tok * k_token_stride + (int64_t)(h - Hq) * B200_HD;
-    __nv_bfloat16* dst = is_q ? q_out + (tok * Hq + h) * B200_HD
-                              : (k_out != nullptr ? k_out + (tok * Hkv + (h - Hq)) * B200_HD : nullptr);
-    const __nv_bfloat16* w = is_q ? q_weight : k_weight;
-    __nv_bfloat16* cache_dst = nullptr;
-    if (STORE && live && !is_q) {
-        const int32_t slot = __ldg(st.slot_mapping + tok);
-        if (slot >= 0)
-            cache_dst = (is_v ? st.v_cache + (int64_t)(h - Hq - Hkv) * B200_HD : st.k_cache + (int64_t)(h - Hq) * B200_HD)
-                        + (int64_t)slot * Hkv * B200_HD;
+    const uint32_t H = STORE ? Hq + 2 * Hkv : Hq + Hkv;
+    const bool has_w = q_weight != nullptr;                    // both weights or neither (checked at the ABI)
+    // weights: the same 2 x 16 bytes for every row of a kind, loaded once
+    int4 wq_lo = make_int4(0, 0, 0, 0), wq_hi = wq_lo, wk_lo = wq_lo, wk_hi = wq_lo;
+    if (has_w) {
+        wq_lo = *reinterpret_cast<const int4*>(q_weight + 8 * sub); wq_hi = *reinterpret_cast<const int4*>(q_weight + 64 + 8 * sub);
+        wk_lo = *reinterpret_cast<const int4*>(k_weight + 8 * sub); wk_hi = *reinterpret_cast<const int4*>(k_weight + 64 + 8 * sub);
     }
-
-    int4 lo4 = make_int4(0, 0, 0, 0), hi4 = lo4;
-    if (live) {
-        lo4 = ld_nc_v4(src + 8 * sub);
-        hi4 = ld_nc_v4(src + 64 + 8 * sub);
-    }
-    if (STORE && is_v) {                                       // v is copied untouched (no shuffles below need it:
-        if (cache_dst != nullptr) {                            //  the butterfly stays inside an 8-lane row group,
-            st_v4(cache_dst + 8 * sub, lo4);                   //  but every lane must still execute it)
-            st_v4(cache_dst + 64 + 8 * sub, hi4);
+    const uint32_t group = (blockIdx.x * 256u + threadIdx.x) >> 3;            // 8-lane row group of this thread
+    const uint32_t groups = gridDim.x * 32u;
+    // rounds of NR_ROWS * groups rows; every lane of a warp runs the same number of rounds (shuffles below)
+    for (uint32_t row0 = group; row0 - group < total_rows; row0 += NR_ROWS * groups) {
+        bool live[NR_ROWS], is_q[NR_ROWS], is_v[NR_ROWS];
+        int4 lo4[NR_ROWS], hi4[NR_ROWS];
+        __nv_bfloat16* dst[NR_ROWS];
+        __nv_bfloat16* cache_dst[NR_ROWS];
+        const float* cs[NR_ROWS];
+#pragma unroll
+        for (int r = 0; r < NR_ROWS; ++r) {
+            const uint32_t row = row0 + r * groups;
+            live[r] = row < total_rows;                        // dead lanes still take part in the shuffles
+            const uint32_t tok = live[r] ? row / H : 0;
+            const uint32_t h = live[r] ? row - tok * H : 0;
+            is_q[r] = h < Hq;
+            is_v[r] = STORE && h >= Hq + Hkv;
+            const __nv_bfloat16* src = is_q[r] ? q + (int64_t)tok * q_token_stride + (int64_t)h * B200_HD
+                                     : is_v[r] ? st.v + (int64_t)tok * st.v_token_stride + (int64_t)(h - Hq - Hkv) * B200_HD
+                                               : k + (int64_t)tok * k_token_stride + (int64_t)(h - Hq) * B200_HD;
+            dst[r] = is_q[r] ? q_out + ((int64_t)tok * Hq + h) * B200_HD
+                             : (k_out != nullptr && !is_v[r] ? k_out + ((int64_t)tok * Hkv + (h - Hq)) * B200_HD : nullptr);
+            lo4[r] = hi4[r] = make_int4(0, 0, 0, 0);
+            cache_dst[r] = nullptr;
+            cs[r] = cos_sin;
+            if (live[r]) {
+                lo4[r] = ld_nc_v4(src + 8 * sub);
+                hi4[r] = ld_nc_v4(src + 64 + 8 * sub);
+                if (!is_v[r]) cs[r] = cos_sin + __ldg(positions + tok) * B200_HD + 8 * sub;   // [cos(64) | sin(64)]
+                if (STORE && !is_q[r]) {
+                    const int32_t slot = __ldg(st.slot_mapping + tok);
+                    if (slot >= 0)
+                        cache_dst[r] = (is_v[r] ? st.v_cache + (int64_t)(h - Hq - Hkv) * B200_HD : st.k_cache + (int64_t)(h - Hq) * B200_HD)
+                                       + (int64_t)slot * Hkv * B200_HD;
+                }
+            }
         }
-    }
-    const uint32_t lo_u[4] = {(uint32_t)lo4.x, (uint32_t)lo4.y, (uint32_t)lo4.z, (uint32_t)lo4.w};
-    const uint32_t hi_u[4] = {(uint32_t)hi4.x, (uint32_t)hi4.y, (uint32_t)hi4.z, (uint32_t)hi4.w};
-    float x1[8], x2[8];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const float2 a = unpack_bf16x2(lo_u[j]), b = unpack_bf16x2(hi_u[j]);
-        x1[2 * j] = a.x; x1[2 * j + 1] = a.y;
-        x2[2 * j] = b.x; x2[2 * j + 1] = b.y;
-    }
-    if (w != nullptr) {                                        // nullptr => rotation only (RotaryEmbedding.forward)
-        float ss = 0.f;
+        for (int r = 0; r < NR_ROWS; ++r) {
+            if (STORE && is_v[r] && cache_dst[r] != nullptr) { // v is copied untouched
+                st_v4(cache_dst[r] + 8 * sub, lo4[r]);
+                st_v4(cache_dst[r] + 64 + 8 * sub, hi4[r]);
+            }
+            const uint32_t lo_u[4] = {(uint32_t)lo4[r].x, (uint32_t)lo4[r].y, (uint32_t)lo4[r].z, (uint32_t)lo4[r].w};
+            const uint32_t hi_u[4] = {(uint32_t)hi4[r].x, (uint32_t)hi4[r].y, (uint32_t)hi4[r].z, (uint32_t)hi4[r].w};
+            float x1[8], x2[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) ss += x1[j] * x1[j] + x2[j] * x2[j];
+            for (int j = 0; j < 4; ++j) {
+                const float2 a = unpack_bf16x2(lo_u[j]), b = unpack_bf16x2(hi_u[j]);
+                x1[2 * j] = a.x; x1[2 * j + 1] = a.y;
+                x2[2 * j] = b.x; x2[2 * j + 1] = b.y;
+            }
+            if (has_w) {                                       // uniform: nullptr => rotation only (RotaryEmbedding.forward)
+                float ss = 0.f;
 #pragma unroll
-        for (int o = 4; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-        const float rstd = rsqrtf(__fadd_rn(ss * (1.0f / B200_HD), eps));
-        const int4 wl4 = *reinterpret_cast<const int4*>(w + 8 * sub);
-        const int4 wh4 = *reinterpret_cast<const int4*>(w + 64 + 8 * sub);
-        const uint32_t wl_u[4] = {(uint32_t)wl4.x, (uint32_t)wl4.y, (uint32_t)wl4.z, (uint32_t)wl4.w};
-        const uint32_t wh_u[4] = {(uint32_t)wh4.x, (uint32_t)wh4.y, (uint32_t)wh4.z, (uint32_t)wh4.w};
-        // bf16(x * rstd) then bf16(that * w): two roundings, as in the reference
-        auto nrm = [&](float x, float wt) {
-            const float y = __bfloat162float(__float2bfloat16_rn(__fmul_rn(x, rstd)));
-            return __bfloat162float(__float2bfloat16_rn(__fmul_rn(y, wt)));
-        };
+                for (int j = 0; j < 8; ++j) ss += x1[j] * x1[j] + x2[j] * x2[j];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const float2 a = unpack_bf16x2(wl_u[j]), b = unpack_bf16x2(wh_u[j]);
-            x1[2 * j] = nrm(x1[2 * j], a.x); x1[2 * j + 1] = nrm(x1[2 * j + 1], a.y);
-            x2[2 * j] = nrm(x2[2 * j], b.x); x2[2 * j + 1] = nrm(x2[2 * j + 1], b.y);
+                for (int o = 4; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+                const float rstd = rsqrtf(__fadd_rn(ss * (1.0f / B200_HD), eps));
+                const int4 wl4 = is_q[r] ? wq_lo : wk_lo, wh4 = is_q[r] ? wq_hi : wk_hi;
+                const uint32_t wl_u[4] = {(uint32_t)wl4.x, (uint32_t)wl4.y, (uint32_t)wl4.z, (uint32_t)wl4.w};
+                const uint32_t wh_u[4] = {(uint32_t)wh4.x, (uint32_t)wh4.y, (uint32_t)wh4.z, (uint32_t)wh4.w};
+                // bf16(x * rstd) then bf16(that * w): two roundings, as in the reference
+                auto nrm = [&](float x, float wt) {
+                    const float y = __bfloat162float(__float2bfloat16_rn(__fmul_rn(x, rstd)));
+                    return __bfloat162float(__float2bfloat16_rn(__fmul_rn(y, wt)));
+                };
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float2 a = unpack_bf16x2(wl_u[j]), b = unpack_bf16x2(wh_u[j]);
+                    x1[2 * j] = nrm(x1[2 * j], a.x); x1[2 * j + 1] = nrm(x1[2 * j + 1], a.y);
+                    x2[2 * j] = nrm(x2[2 * j], b.x); x2[2 * j + 1] = nrm(x2[2 * j + 1], b.y);
+                }
+            }
+            if (!live[r] || is_v[r]) continue;
+            const float4 c0 = *reinterpret_cast<const float4*>(cs[r]), c1 = *reinterpret_cast<const float4*>(cs[r] + 4);
+            const float4 s0 = *reinterpret_cast<const float4*>(cs[r] + 64), s1 = *reinterpret_cast<const float4*>(cs[r] + 68);
+            const float c[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+            const float s[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+            uint32_t y1[4], y2[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                // y1 = x1*cos - x2*sin ; y2 = x2*cos + x1*sin  (un-fused, matching eager fp32)
+                const int a = 2 * j, b = 2 * j + 1;
+                y1[j] = pack_bf16x2(__fsub_rn(__fmul_rn(x1[a], c[a]), __fmul_rn(x2[a], s[a])),
+                                    __fsub_rn(__fmul_rn(x1[b], c[b]), __fmul_rn(x2[b], s[b])));
+                y2[j] = pack_bf16x2(__fadd_rn(__fmul_rn(x2[a], c[a]), __fmul_rn(x1[a], s[a])),
+                                    __fadd_rn(__fmul_rn(x2[b], c[b]), __fmul_rn(x1[b], s[b])));
+            }
+            const int4 o_lo = make_int4(y1[0], y1[1], y1[2], y1[3]), o_hi = make_int4(y2[0], y2[1], y2[2], y2[3]);
+            if (dst[r] != nullptr) {
+                st_v4(dst[r] + 8 * sub, o_lo);
+                st_v4(dst[r] + 64 + 8 * sub, o_hi);
+            }
+            if (STORE && cache_dst[r] != nullptr) {
+                st_v4(cache_dst[r] + 8 * sub, o_lo);
+                st_v4(cache_dst[r] + 64 + 8 * sub, o_hi);
+            }
         }
-    }
-    if (!live || is_v) return;
-    const float* cs = cos_sin + positions[tok] * B200_HD + 8 * sub;       // [cos(64) | sin(64)]
-    const float4 c0 = *reinterpret_cast<const float4*>(cs), c1 = *reinterpret_cast<const float4*>(cs + 4);
-    const float4 s0 = *reinterpret_cast<const float4*>(cs + 64), s1 = *reinterpret_cast<const float4*>(cs + 68);
-    const float c[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
-    const float s[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
-    uint32_t y1[4], y2[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        // y1 = x1*cos - x2*sin ; y2 = x2*cos + x1*sin  (un-fused, matching eager fp32)
-        const int a = 2 * j, b = 2 * j + 1;
-        y1[j] = pack_bf16x2(__fsub_rn(__fmul_rn(x1[a], c[a]), __fmul_rn(x2[a], s[a])),
-                            __fsub_rn(__fmul_rn(x1[b], c[b]), __fmul_rn(x2[b], s[b])));
-        y2[j] = pack_bf16x2(__fadd_rn(__fmul_rn(x2[a], c[a]), __fmul_rn(x1[a], s[a])),
-                            __fadd_rn(__fmul_rn(x2[b], c[b]), __fmul_rn(x1[b], s[b])));
-    }
-    const int4 o_lo = make_int4(y1[0], y1[1], y1[2], y1[3]), o_hi = make_int4(y2[0], y2[1], y2[2], y2[3]);
-    if (dst != nullptr) {
-        st_v4(dst + 8 * sub, o_lo);
-        st_v4(dst + 64 + 8 * sub, o_hi);
-    }
-    if (STORE && cache_dst != nullptr) {
-        st_v4(cache_dst + 8 * sub, o_lo);
-        st_v4(cache_dst + 64 + 8 * sub, o_hi);
     }
 }
 
@@ -256,60 +303,47 @@ static inline int grid_for(int64_t threads_needed, int block, int waves_cap = 8)
 int launch_kv_scatter(const void* key, const void* value, int64_t key_row_stride, int64_t value_row_stride,
                       void* k_cache, void* v_cache, const int32_t* slot_mapping,
                       int32_t T, int32_t Hkv, int32_t D, cudaStream_t stream) {
-    const int32_t row_bytes = Hkv * D * 2;
-    const int32_t chunks = row_bytes / 16;
-    int lg = 0;
-    while ((1 << lg) < chunks) ++lg;
-    if ((1 << lg) != chunks) {
-        // non power-of-two rows (e.g. 5 heads): fall back to one "row" per head
-        return launch_kv_scatter_generic(key, value, key_row_stride, value_row_stride, k_cache, v_cache,
-                                         slot_mapping, T, Hkv, D, stream);
-    }
+    const uint32_t chunks = (uint32_t)(Hkv * D * 2 / 16);
+    uint32_t lg = 0;
+    while ((1u << lg) < chunks) ++lg;
     const int64_t total = (int64_t)T * chunks;
-    kv_scatter_kernel<<<grid_for(total, 256), 256, 0, stream>>>(
-        (const uint8_t*)key, (const uint8_t*)value, key_row_stride * 2, value_row_stride * 2,
-        (uint8_t*)k_cache, (uint8_t*)v_cache, slot_mapping, total, lg);
+    if (total >= (int64_t)1 << 32) return -5;                     // 64 GB of K rows in one call: not a real shape
+    const int grid = grid_for((total + SC_UNROLL - 1) / SC_UNROLL, 256);
+    if ((1u << lg) == chunks)
+        kv_scatter_kernel<true><<<grid, 256, 0, stream>>>(
+            (const uint8_t*)key, (const uint8_t*)value, key_row_stride * 2, value_row_stride * 2,
+            (uint8_t*)k_cache, (uint8_t*)v_cache, slot_mapping, (uint32_t)total, chunks, lg);
+    else                                                          // non power-of-two rows (e.g. 5 heads)
+        kv_scatter_kernel<false><<<grid, 256, 0, stream>>>(
+            (const uint8_t*)key, (const uint8_t*)value, key_row_stride * 2, value_row_stride * 2,
+            (uint8_t*)k_cache, (uint8_t*)v_cache, slot_mapping, (uint32_t)total, chunks, lg);
     return (int)cudaGetLastError();
-}
-
-__global__ void __launch_bounds__(256) kv_scatter_generic_kernel(
-    const uint8_t* __restrict__ key, const uint8_t* __restrict__ value, int64_t key_row_bytes, int64_t value_row_bytes,
-    uint8_t* __restrict__ k_cache, uint8_t* __restrict__ v_cache, const int32_t* __restrict__ slot_mapping,
-    int64_t total_chunks, int32_t chunks_per_row) {
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_chunks; i += stride) {
-        const int64_t tok = i / chunks_per_row;
-        const int64_t c = i - tok * chunks_per_row;
-        const int32_t slot = __ldg(slot_mapping + tok);
-        if (slot < 0) continue;
-        const int4 kv = ld_nc_v4(key + tok * key_row_bytes + c * 16);
-        const int4 vv = ld_nc_v4(value + tok * value_row_bytes + c * 16);
-        const int64_t dst = ((int64_t)slot * chunks_per_row + c) * 16;
-        st_v4(k_cache + dst, kv);
-        st_v4(v_cache + dst, vv);
-    }
 }
 
 int launch_kv_scatter_generic(const void* key, const void* value, int64_t key_row_stride, int64_t value_row_stride,
                               void* k_cache, void* v_cache, const int32_t* slot_mapping,
                               int32_t T, int32_t Hkv, int32_t D, cudaStream_t stream) {
-    const int32_t chunks = Hkv * D * 2 / 16;
-    const int64_t total = (int64_t)T * chunks;
-    kv_scatter_generic_kernel<<<grid_for(total, 256), 256, 0, stream>>>(
-        (const uint8_t*)key, (const uint8_t*)value, key_row_stride * 2, value_row_stride * 2,
-        (uint8_t*)k_cache, (uint8_t*)v_cache, slot_mapping, total, chunks);
-    return (int)cudaGetLastError();
+    return launch_kv_scatter(key, value, key_row_stride, value_row_stride, k_cache, v_cache, slot_mapping, T, Hkv, D, stream);
+}
+
+// rows are spread over at most 8 CTAs per SM (the grid-stride loop takes the rest): enough CTAs to fill
+// the machine, few enough that a 16k-token prefill is not 25k tiny CTAs
+static inline int norm_rope_grid(int64_t rows) {
+    int64_t blocks = (rows + 32 * NR_ROWS - 1) / (32 * NR_ROWS);  // 32 rows per CTA per round
+    const int64_t cap = (int64_t)sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    return (int)(blocks < 1 ? 1 : blocks);
 }
 
 int launch_qk_norm_rope(const void* q, int64_t q_token_stride, const void* k, int64_t k_token_stride,
                         const int64_t* positions, const float* cos_sin, const void* qw, const void* kw, float eps,
                         void* q_out, void* k_out, int32_t T, int32_t Hq, int32_t Hkv, cudaStream_t stream) {
     const int64_t rows = (int64_t)T * (Hq + Hkv);
-    const int64_t blocks = (rows + 31) / 32;                      // 8 lanes per row, 256 threads
-    qk_norm_rope_kernel<false><<<(unsigned)blocks, 256, 0, stream>>>(
+    if (rows >= (int64_t)1 << 31) return -5;
+    qk_norm_rope_kernel<false><<<norm_rope_grid(rows), 256, 0, stream>>>(
         (const __nv_bfloat16*)q, q_token_stride, (const __nv_bfloat16*)k, k_token_stride, positions, cos_sin,
         (const __nv_bfloat16*)qw, (const __nv_bfloat16*)kw, eps, (__nv_bfloat16*)q_out, (__nv_bfloat16*)k_out,
-        rows, Hq, Hkv, KvStoreArgs{});
+        (uint32_t)rows, (uint32_t)Hq, (uint32_t)Hkv, KvStoreArgs{});
     return (int)cudaGetLastError();
 }
 
@@ -319,14 +353,14 @@ int launch_qk_norm_rope_store(const void* q, int64_t q_token_stride, const void*
                               void* q_out, void* k_out, void* k_cache, void* v_cache, const int32_t* slot_mapping,
                               int32_t T, int32_t Hq, int32_t Hkv, cudaStream_t stream) {
     const int64_t rows = (int64_t)T * (Hq + 2 * Hkv);
-    const int64_t blocks = (rows + 31) / 32;
+    if (rows >= (int64_t)1 << 31) return -5;
     KvStoreArgs st;
     st.v = (const __nv_bfloat16*)v; st.v_token_stride = v_token_stride;
     st.k_cache = (__nv_bfloat16*)k_cache; st.v_cache = (__nv_bfloat16*)v_cache; st.slot_mapping = slot_mapping;
-    qk_norm_rope_kernel<true><<<(unsigned)blocks, 256, 0, stream>>>(
+    qk_norm_rope_kernel<true><<<norm_rope_grid(rows), 256, 0, stream>>>(
         (const __nv_bfloat16*)q, q_token_stride, (const __nv_bfloat16*)k, k_token_stride, positions, cos_sin,
         (const __nv_bfloat16*)qw, (const __nv_bfloat16*)kw, eps, (__nv_bfloat16*)q_out, (__nv_bfloat16*)k_out,
-        rows, Hq, Hkv, st);
+        (uint32_t)rows, (uint32_t)Hq, (uint32_t)Hkv, st);
     return (int)cudaGetLastError();
 }
 

@@ -62,7 +62,7 @@ def test_decode_plan_is_static_and_bounded(lib):
     assert 2 <= s <= 64
     assert lib.b200_decode_plan(1, 8, 300) <= 2              # never finer than one page per split
     assert lib.b200_decode_workspace_bytes(4, 32, 1) == 0
-    assert lib.b200_decode_workspace_bytes(4, 32, 3) == 4 * 3 * 32 * 129 * 4
+    assert lib.b200_decode_workspace_bytes(4, 32, 3) == 64 * 1024 + 4 * 3 * 32 * 129 * 4   # tickets + partial O + LSE
 
 
 def test_ops_refuse_cpu_tensors(lib):
