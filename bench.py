@@ -18,6 +18,15 @@ fixed, so "scaling" is "strong" and `value` = bytes all ranks processed / max-ov
   roofline ...... paged_decode_kernel alone, timed live with CUDA events on its stream
   cpu_baseline .. the CPU oracle port (pure torch, all host threads) on a bounded sample
 
+  prefill ....... second part of BASELINE.json's metric: persistent tcgen05 prefill TFLOP/s on 4 x 4096 causal at this
+                  rank's head counts, plus BASELINE configs[4]'s own shape (32k shared prefix + 63 branches, 8q/1kv)
+  gpu_baseline .. the UNMODIFIED reference Attention.forward (baseline/_ref: Triton + flash-attn 2.8.3) on the
+                  identical tensors, timed in a subprocess (tools/ref_attention_bench.py)
+  allreduce ..... N > 1: parity and us per CUDA-graph-replayed call of the peer-memory all-reduce and of the NVLS
+                  all-reduce fused with add+RMSNorm, next to NCCL (+ the separate RMSNorm kernel), 2 MB message
+  tok_per_s ..... third part of the metric: Qwen3-8B (random-init) 256 x 128-in/256-out through the untouched
+                  LLM.generate at TP = N, reference arm and drop-in arm, median of 3 passes (tools/e2e_generate.py)
+
 `--impl reference` times that CPU port alone (the reference has no CPU implementation of this
 path: its Triton + flash-attn kernels are CUDA-only), as the contract's reference arm.
 """
@@ -53,6 +62,18 @@ def peaks():
             return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, copy burst)"
     except Exception:
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def measured_traffic(hq, hkv):
+    """dram__bytes_read + dram__bytes_write per launch of paged_decode_kernel from an `ncu --set full` capture of
+    THIS shape (profiles/decode_traffic.json, keyed by per-rank heads), or None when that shape was never captured
+    (a constant printed next to another shape's algorithmic bytes would read as wasted traffic)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "decode_traffic.json")) as f:
+            rec = json.load(f)
+        return rec.get("shapes", {}).get(f"b{B}_ctx{CTX}_{hq}q{hkv}kv", {}).get("dram_bytes_per_launch")
+    except Exception:
+        return None
 
 
 class ClockSampler(threading.Thread):
@@ -223,7 +244,11 @@ def run_ours(args):
         decode_only()
     ms_decode = timed(decode_only, args.steps) / args.steps
     reset_context()
-    prefill = prefill_leg(ops, device, hq, hkv, scale, timed, world) if not args.no_prefill else None
+    prefill = None
+    if not args.no_prefill:
+        prefill = prefill_leg(ops, device, hq, hkv, scale, timed, world)
+        prefill["cfg5"] = prefill_cfg5_leg(ops, device, scale, timed)
+    allreduce = allreduce_leg(ops, device, rank, world, timed) if world > 1 and not args.no_allreduce else None
 
     dec_b, sc_b = algorithmic_bytes(B, CTX, hq, hkv)
     total_bytes = (dec_b + sc_b) * world
@@ -232,40 +257,231 @@ def run_ours(args):
     e2e_value = total_bytes / (ms_e2e / args.steps * 1e-3) / 1e9
     peak, peak_src = peaks()
     achieved = dec_b / (ms_decode * 1e-3) / 1e9                      # per GPU
-    launches_per_step = 2 + (1 if num_splits > 1 else 0)
+    fused = os.environ.get("B200ATTN_DECODE_FUSED_REDUCE", "1") != "0"
+    launches_per_step = 2 + (1 if (num_splits > 1 and not fused) else 0)
 
-    if rank == 0:
-        cpu = cpu_baseline_sample() if world == 1 and not args.no_cpu_baseline else None
-        traffic = None
-        try:
-            with open(os.path.join(ROOT, "profiles", "decode_traffic.json")) as f:
-                traffic = json.load(f).get("dram_bytes_per_launch")
-        except Exception:
-            pass
-        line = {
-            "metric": METRIC, "value": round(value, 1), "unit": "GB/s", "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": round(ms_step, 4), "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "batch": B, "context_len": CTX, "q_heads": HQ, "kv_heads": HKV,
-                       "head_dim": D, "page": PAGE, "sharding": f"tp{world} (heads; no collective on this path)",
-                       "step": "Attention.forward = kv_scatter + paged decode (+reduce)", "num_splits": num_splits,
-                       "l2": "inputs larger than L2 (K/V working set %.2f GB per GPU vs 126 MB L2)" % (dec_b / 1e9)},
-            "e2e": {"value": round(e2e_value, 1), "unit": "GB/s", "h2d_bytes_per_step": h2d * world,
-                    "d2h_bytes_per_step": d2h * world, "ms_per_step": round(ms_e2e / args.steps, 4)},
-            "gpu_launches": launches_per_step * args.steps,
-            "roofline": {"kernel": "paged_decode_kernel", "bound": "hbm", "achieved": round(achieved, 1),
-                         "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic,
-                         "peak_source": peak_src, "algorithmic_bytes_per_launch": dec_b,
-                         "ms_per_launch": round(ms_decode, 4), "frac_of_nominal_8TBps": round(achieved / 8000.0, 4)},
-            "cpu_baseline": cpu,
-            "prefill": prefill,
-            "clocks": clocks,
-        }
-        sys.stdout.flush()
-        os.dup2(saved_stdout, 1)
-        print(json.dumps(line), flush=True)
+    # GPU baseline: every rank times the unmodified reference Attention.forward on ITS shard in a subprocess
+    gpu_base = None
+    if not args.no_gpu_baseline:
+        mine = gpu_baseline_leg(rank, world, local, args)
+        ms_ref = float(mine.get("ms_per_step", 0.0)) if "ms_per_step" in mine else -1.0
+        if world > 1:
+            t = torch.tensor([ms_ref, -ms_ref], device=device, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            worst, best = t[0].item(), -t[1].item()
+            ms_ref = worst if best > 0 else -1.0                   # any rank without a number => no aggregate
+        if ms_ref > 0:
+            ref_value = total_bytes / (ms_ref * 1e-3) / 1e9
+            gpu_base = {"impl": mine.get("impl"), "flash_attn": mine.get("flash_attn"), "value": round(ref_value, 1),
+                        "unit": "GB/s", "ms_per_step": round(ms_ref, 4), "speedup": round(value / ref_value, 3),
+                        "how": "same seeded tensors, same step (scatter + paged decode of one layer), subprocess per rank, "
+                               "CUDA events, max over ranks"}
+        else:
+            gpu_base = {"unavailable": mine.get("unavailable") or mine.get("error") or "no number from some rank"}
+
     if world > 1:
+        ops.shutdown_collectives()                                 # b200_ar_destroy / b200_nvls_destroy (collective)
+        dist.barrier()
         dist.destroy_process_group()
+    if rank != 0:
+        return                                                     # rank 0 alone runs the engine-level leg and prints
+
+    cpu = cpu_baseline_sample() if world == 1 and not args.no_cpu_baseline else None
+    traffic = measured_traffic(hq, hkv)
+    line = {
+        "metric": METRIC, "value": round(value, 1), "unit": "GB/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": round(ms_step, 4), "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "batch": B, "context_len": CTX, "q_heads": HQ, "kv_heads": HKV,
+                   "head_dim": D, "page": PAGE, "sharding": f"tp{world} (heads; no collective on this path)",
+                   "step": "Attention.forward = kv_scatter + paged decode (split merge inside the decode launch)",
+                   "num_splits": num_splits,
+                   "l2": "inputs larger than L2 (K/V working set %.2f GB per GPU vs 126 MB L2)" % (dec_b / 1e9)},
+        "e2e": {"value": round(e2e_value, 1), "unit": "GB/s", "h2d_bytes_per_step": h2d * world,
+                "d2h_bytes_per_step": d2h * world, "ms_per_step": round(ms_e2e / args.steps, 4)},
+        "gpu_launches": launches_per_step * args.steps,
+        "roofline": {"kernel": "paged_decode_kernel", "bound": "hbm", "achieved": round(achieved, 1),
+                     "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic,
+                     "peak_source": peak_src, "algorithmic_bytes_per_launch": dec_b,
+                     "ms_per_launch": round(ms_decode, 4), "frac_of_nominal_8TBps": round(achieved / 8000.0, 4)},
+        "cpu_baseline": cpu,
+        "gpu_baseline": gpu_base,
+        "prefill": prefill,
+        "allreduce": allreduce,
+        "clocks": clocks,
+    }
+    # engine-level leg: frees this process's device memory first (the engine sizes its KV cache from what is free)
+    del pr, attn, bt_d, cl_d, sm_d, qkv_d, q_d, k_d, v_d, q_c, k_c, d_qkv, d_sm, d_cl, d_bt
+    ops._WS_CACHE.clear()
+    torch.cuda.empty_cache()
+    if not args.no_tok_per_s:
+        line["tok_per_s"] = tok_per_s_leg(world, local)
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
+    print(json.dumps(line), flush=True)
+
+
+def _clean_env():
+    """Environment for engine subprocesses: no torchrun rendezvous variables (the reference engine spawns its own
+    tensor-parallel workers and rendezvous, llm_engine.py:103-109, model_runner.py:121)."""
+    env = dict(os.environ)
+    for k in list(env):
+        if k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "LOCAL_WORLD_SIZE", "GROUP_RANK", "GROUP_WORLD_SIZE", "ROLE_RANK",
+                 "ROLE_WORLD_SIZE", "ROLE_NAME", "MASTER_ADDR", "MASTER_PORT", "OMP_NUM_THREADS") or k.startswith("TORCHELASTIC_"):
+            env.pop(k)
+    return env
+
+
+def _last_json_line(text):
+    for ln in reversed(text.strip().splitlines()):
+        ln = ln.strip()
+        if ln.startswith("{") and ln.endswith("}"):
+            try:
+                return json.loads(ln)
+            except Exception:
+                continue
+    return None
+
+
+def gpu_baseline_leg(rank, world, local, args):
+    import subprocess
+    cmd = [sys.executable, os.path.join(ROOT, "tools", "ref_attention_bench.py"), "--rank", str(rank), "--world", str(world),
+           "--device", str(local), "--steps", str(args.steps), "--warmup", str(max(args.warmup, 3))]
+    try:
+        r = subprocess.run(cmd, env=_clean_env(), capture_output=True, text=True, timeout=600)
+        rec = _last_json_line(r.stdout)
+        if r.returncode != 0 or rec is None:
+            return {"error": f"rc {r.returncode}: {(r.stderr or r.stdout)[-300:]}"}
+        return rec
+    except Exception as exc:                                       # noqa: BLE001
+        return {"error": f"{type(exc).__name__}: {exc}"}
+
+
+def tok_per_s_leg(world, local, passes=3):
+    """Qwen3-8B (synthetic dir, seeded random weights) 256 x 128-in / 256-out, chunked prefill, CUDA graphs on, through the
+    reference's untouched LLM.generate at TP = `world`: reference arm (baseline/_ref as shipped) then drop-in arm, the
+    same harness for both (tools/e2e_generate.py, tools/e2e/sitecustomize.py).  tok/s = generated tokens / wall time of
+    generate() (the reference's bench.py:26-27); median of `passes` passes after one discarded pass; clocks sampled."""
+    import subprocess
+    import tempfile
+    out = {"model": "qwen3-8b (random-init)", "workload": "256 seqs x 128 in / 256 out, chunked prefill, temperature 0.6",
+           "tp": world, "passes": passes, "statistic": "median of passes 2..N+1 (pass 1 discarded: re-traces, first-touch)"}
+    if not os.path.isdir(os.path.join(ROOT, "baseline", "_ref", "nanovllm")):
+        out["unavailable"] = "baseline/_ref (offline install of the reference) is not in this tree"
+        return out
+    tmp = tempfile.mkdtemp(prefix="b200_bench_")
+    for arm in ("reference", "dropin"):
+        path = os.path.join(tmp, f"{arm}.json")
+        cmd = [sys.executable, os.path.join(ROOT, "tools", "e2e_generate.py"), "--arm", arm, "--size", "8b", "--tp", str(world),
+               "--num-seqs", "256", "--in-len", "128", "--out-len", "256", "--chunked-prefill", "--repeat", str(passes + 1),
+               "--out", path]
+        sampler = ClockSampler(local)
+        sampler.start()
+        try:
+            r = subprocess.run(cmd, env=_clean_env(), capture_output=True, text=True, timeout=900)
+            clocks = sampler.finish()
+            if r.returncode != 0 or not os.path.exists(path):
+                out[arm] = {"error": f"rc {r.returncode}: {(r.stderr or r.stdout)[-400:]}"}
+                continue
+            with open(path) as f:
+                rec = json.load(f)
+            secs = sorted(rec["seconds_all"][1:] or rec["seconds_all"])
+            med = secs[len(secs) // 2]
+            out[arm] = {"tok_per_s": round(rec["generated_tokens"] / med, 1), "seconds_median": round(med, 4),
+                        "seconds_all": [round(x, 4) for x in rec["seconds_all"]], "init_seconds": round(rec["init_seconds"], 2),
+                        "dropin_installed": rec["dropin_installed"], "clocks": clocks}
+        except Exception as exc:                                   # noqa: BLE001
+            sampler.finish()
+            out[arm] = {"error": f"{type(exc).__name__}: {exc}"}
+    try:
+        out["speedup"] = round(out["dropin"]["tok_per_s"] / out["reference"]["tok_per_s"], 3)
+    except Exception:                                              # noqa: BLE001
+        out["speedup"] = None
+    return out
+
+
+def allreduce_leg(ops, device, rank, world, timed, tokens=256, hidden=4096, calls=20, replays=5):
+    """SURVEY 8 f3 under the driver's eyes: the decode-sized RowParallelLinear message ([256, 4096] bf16 = 2 MB).
+    (1) peer-memory all-reduce (ops.tp_all_reduce_) vs dist.all_reduce: bit-identical on all ranks and equal to the
+    fp32 sum in rank order rounded once; (2) NVLS launch = all-reduce + residual add + RMSNorm vs dist.all_reduce
+    followed by the separate RMSNorm kernel: identical on all ranks, residual within 1 bf16 ulp (the switch's summation
+    order is its own), normed output within 2; (3) us per call, CUDA-graph replayed, all four."""
+    import torch.distributed as dist
+    res = {"message_bytes": tokens * hidden * 2, "tokens": tokens, "hidden": hidden, "world": world}
+    try:
+        g = torch.Generator(device=device).manual_seed(1234 + rank)
+        x = torch.randn(tokens, hidden, generator=g, device=device).bfloat16()
+        gs = torch.Generator(device=device).manual_seed(99)              # identical on every rank
+        resid = torch.randn(tokens, hidden, generator=gs, device=device).bfloat16()
+        w = (1 + 0.1 * torch.randn(hidden, generator=gs, device=device)).bfloat16()
+        allx = [torch.empty_like(x) for _ in range(world)]
+        dist.all_gather(allx, x)
+        exact = torch.stack([t.float() for t in allx]).sum(0)            # fp32, rank order
+        once = exact.bfloat16()
+        nccl = x.clone()
+        dist.all_reduce(nccl)
+
+        def same_on_all_ranks(t):
+            h = t.view(torch.int16).to(torch.int64).sum().reshape(1)
+            lo, hi = h.clone(), h.clone()
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+            return bool((lo == hi).item())
+
+        def ulps(a, b):
+            bf = b.float()
+            ulp = torch.pow(2.0, torch.floor(torch.log2(bf.abs().clamp_min(2.0 ** -126))) - 7)
+            return float(((a.float() - bf).abs() / ulp).max().item())
+
+        ours = x.clone()
+        ops.tp_all_reduce_(ours)
+        peer_ok = bool(torch.equal(ours, once)) and same_on_all_ranks(ours)
+        res["peer_memory"] = {"parity_ok": peer_ok, "equals_fp32_sum_rounded_once": bool(torch.equal(ours, once)),
+                              "identical_on_all_ranks": same_on_all_ranks(ours), "max_ulps_vs_nccl": ulps(ours, nccl),
+                              "form": ops._TP_AR.choose_form(x.numel() * 2) if ops._TP_AR else None}
+        want_y, want_r = ops.rms_norm(nccl, w, 1e-6, resid.clone())       # dist.all_reduce -> add + RMSNorm kernel
+        nv = ops.tp_nvls()
+        if nv:
+            for one_shot in (False, True):
+                r2 = resid.clone()
+                y, _ = nv.all_reduce_add_rms_norm(x, r2, w, 1e-6, one_shot=one_shot)
+                key = "nvls_fused_one_shot" if one_shot else "nvls_fused_two_shot"
+                ident = same_on_all_ranks(y) and same_on_all_ranks(r2)
+                ur, uy = ulps(r2, want_r), ulps(y, want_y)
+                res[key] = {"parity_ok": bool(ident and ur <= 1.0 and uy <= 2.0), "identical_on_all_ranks": ident,
+                            "residual_max_ulps_vs_nccl_path": ur, "normed_max_ulps_vs_nccl_path": uy,
+                            "status": nv.status()}
+            res["nvls_default_form"] = "one_shot" if nv.one_shot(x.numel() * 2) else "two_shot"
+        else:
+            res["nvls_fused"] = {"unavailable": "no NVLS multicast mapping for this group (peer-store form in use)"}
+
+        def graph_us(fn):
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                fn()
+            torch.cuda.current_stream().wait_stream(side)
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr):
+                for _ in range(calls):
+                    fn()
+            gr.replay()
+            return timed(gr.replay, replays) / (replays * calls) * 1e3
+
+        buf, rbuf, ybuf = x.clone(), resid.clone(), torch.empty_like(x)
+        lat = {"nccl_all_reduce": graph_us(lambda: dist.all_reduce(buf)),
+               "peer_memory_all_reduce": graph_us(lambda: ops.tp_all_reduce_(buf))}
+        lat["nccl_all_reduce_plus_rmsnorm_kernel"] = graph_us(lambda: (dist.all_reduce(buf), ops.rms_norm(buf, w, 1e-6, rbuf)))
+        lat["peer_memory_all_reduce_plus_rmsnorm_kernel"] = graph_us(lambda: (ops.tp_all_reduce_(buf), ops.rms_norm(buf, w, 1e-6, rbuf)))
+        if nv:
+            lat["nvls_fused_two_shot"] = graph_us(lambda: nv.all_reduce_add_rms_norm(buf, rbuf, w, 1e-6, one_shot=False, out=ybuf))
+            lat["nvls_fused_one_shot"] = graph_us(lambda: nv.all_reduce_add_rms_norm(buf, rbuf, w, 1e-6, one_shot=True, out=ybuf))
+        res["us_per_call_graph_replay"] = {k: round(v, 2) for k, v in lat.items()}
+        res["parity_ok"] = bool(peer_ok and all(v.get("parity_ok", True) for k, v in res.items()
+                                                if isinstance(v, dict) and k.startswith("nvls_fused_")))
+    except Exception as exc:                                           # noqa: BLE001 -- the headline line must still print
+        res["error"] = f"{type(exc).__name__}: {exc}"
+    return res
 
 
 def prefill_leg(ops, device, hq, hkv, scale, timed, world, seqs=4, seqlen=4096, iters=20):
@@ -296,6 +512,48 @@ def prefill_leg(ops, device, hq, hkv, scale, timed, world, seqs=4, seqlen=4096, 
     return {"kernel": "prefill_persist_kernel", "workload": f"{seqs}x{seqlen} causal, {hq}q/{hkv}kv per GPU", "bound": "tensor",
             "achieved": round(tf * world, 1), "per_gpu": round(tf, 1), "peak": peak, "unit": "TFLOP/s",
             "frac": round(tf / peak, 4), "peak_source": src, "ms_per_launch": round(ms, 4), "flops_per_launch": flops}
+
+
+def prefill_cfg5_leg(ops, device, scale, timed, iters=5):
+    """BASELINE.json configs[4] at its own per-rank shape (Qwen3-32B at TP=8: 8 q / 1 kv head): one step of the
+    long-context prefix-caching workload -- row 0 computes the whole 32,832-token prompt, 63 branch rows compute
+    their 64-token tails against the same 128 cached prefix pages (paged, bottom-right causal).  pairs =
+    671,238,144 => 2.75 TFLOP per layer per rank."""
+    hq, hkv, prefix, tail, branches = 8, 1, 32768, 64, 64
+    lens_q = [prefix + tail] + [tail] * (branches - 1)
+    lens_k = [prefix + tail] * branches
+    shared = prefix // PAGE
+    nblk = shared + branches
+    g = torch.Generator(device=device).manual_seed(11)
+    kc = torch.randn(nblk, PAGE, hkv, D, generator=g, device=device, dtype=torch.bfloat16)
+    vc = torch.randn(nblk, PAGE, hkv, D, generator=g, device=device, dtype=torch.bfloat16)
+    bt = torch.empty(branches, shared + 1, dtype=torch.int32)
+    bt[:, :shared] = torch.arange(shared, dtype=torch.int32)
+    bt[:, shared] = torch.arange(shared, shared + branches, dtype=torch.int32)
+    bt = bt.to(device)
+    T = sum(lens_q)
+    q = torch.randn(T, hq, D, generator=g, device=device, dtype=torch.bfloat16)
+    cu_q = torch.tensor([0] + torch.tensor(lens_q).cumsum(0).tolist(), dtype=torch.int32, device=device)
+    cu_k = torch.tensor([0] + torch.tensor(lens_k).cumsum(0).tolist(), dtype=torch.int32, device=device)
+    plan = ops.attn_plan(cu_q, cu_k, T, hq, hkv, route_decode=True)
+    out = torch.empty_like(q)
+
+    def run():
+        ops.attn_varlen_planned(q, kc, vc, cu_q, cu_k, max(lens_q), max(lens_k), scale, block_table=bt, plan=plan, out=out)
+    for _ in range(3):
+        run()
+    ms = timed(run, iters) / iters
+    pairs = sum(lq * (lk - lq) + lq * (lq + 1) // 2 for lq, lk in zip(lens_q, lens_k))
+    flops = 4 * D * hq * pairs
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peak = float(json.load(f)["bf16_tflops"])
+    except Exception:
+        peak = 1590.0
+    tf = flops / (ms * 1e-3) / 1e12
+    return {"workload": "configs[4]: 32,768-token shared prefix + 64 branches of 64 tokens, 8q/1kv (32B at TP8), paged",
+            "per_gpu": round(tf, 1), "unit": "TFLOP/s", "peak": peak, "frac": round(tf / peak, 4),
+            "ms_per_launch": round(ms, 4), "flops_per_launch": flops}
 
 
 def cpu_baseline_sample(num_seqs=32, reps=2):
@@ -358,11 +616,14 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-prefill", action="store_true")
+    ap.add_argument("--no-allreduce", action="store_true", help="skip the N > 1 all-reduce parity/latency leg")
+    ap.add_argument("--no-gpu-baseline", action="store_true", help="skip the reference Attention.forward (flash-attn) subprocess")
+    ap.add_argument("--no-tok-per-s", action="store_true", help="skip the Qwen3-8B LLM.generate leg (both arms)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -193,7 +193,52 @@ def run(self, seqs, _get_context, _reset_context):
 # All a worker needs is the packed metadata arena rank 0 builds anyway, so rank 0 sends THAT (one bytes
 # object + a tiny layout) as a "run_packed" call; workers upload it and run the forward.  Message
 # format, mailbox, events and the `loop`/`read_shm`/`write_shm` methods are the reference's, untouched.
+# An arena larger than the reference's 1 MiB mailbox travels through a side shared-memory segment
+# (the reference's own message would overflow there too): the cap is lifted, not inherited.
 _MAILBOX_HEADROOM = 4096
+_ARENA_NAME = "nanovllm_b200_arena"
+
+
+def _shared_memory(name, create=False, size=0):
+    from multiprocessing.shared_memory import SharedMemory
+    if create:
+        try:                                              # a crashed run may have left the segment behind (the
+            stale = SharedMemory(name=name)               # reference cleans up its own the same way, model_runner.py:148-157)
+            stale.close()
+            stale.unlink()
+        except FileNotFoundError:
+            pass
+    return SharedMemory(name=name, create=create, size=size)
+
+
+def _side_arena(self, nbytes):
+    """Rank 0: a shared-memory segment of at least `nbytes` for arenas the reference's 1 MiB mailbox
+    (model_runner.py:160) cannot carry (the reference itself overflows there).  Grown by
+    doubling under a new name; workers attach by the name that travels in the message."""
+    cur = getattr(self, "_b200_arena", None)
+    if cur is None or cur.size < nbytes:
+        gen = getattr(self, "_b200_arena_gen", 0) + 1
+        self._b200_arena_gen = gen
+        size = max(1 << 22, 1 << (int(nbytes) - 1).bit_length() + 1)
+        new = _shared_memory(f"{_ARENA_NAME}_{gen}", create=True, size=size)
+        if cur is not None:
+            cur.close()
+            cur.unlink()
+        cur = self._b200_arena = new
+    return cur
+
+
+def release_side_arena(self):
+    """Close (and, on rank 0, unlink) the side arena; called from the patched ModelRunner.exit."""
+    cur = getattr(self, "_b200_arena", None)
+    if cur is not None:
+        self._b200_arena = None
+        cur.close()
+        if getattr(self, "rank", 0) == 0:
+            try:
+                cur.unlink()
+            except FileNotFoundError:
+                pass
 
 
 def call(self, method_name, *args, _reference_call=None):
@@ -203,18 +248,41 @@ def call(self, method_name, *args, _reference_call=None):
         layout, nbytes, host = _pack(self, arrays)
         if nbytes + _MAILBOX_HEADROOM <= self.shm.size:
             self.write_shm("run_packed", layout, nbytes, max_q, max_k, host.numpy()[:nbytes].tobytes())
-            self._b200_prebuilt = (seqs, layout, nbytes, host, max_q, max_k, arrays["seq_need_compute_logits"].tolist())
-            return self.run(seqs)
-        # too large for the mailbox: the reference's own message (it would overflow there as well)
+        else:
+            # larger than the reference's mailbox: the arena travels through a side segment, only its name
+            # and layout through the mailbox.  Lock-step is the reference's own: rank 0 cannot finish this
+            # step (its forward holds collectives with every worker) before each worker copied the arena out.
+            arena = _side_arena(self, nbytes)
+            arena.buf[:nbytes] = host.numpy()[:nbytes].data
+            self.write_shm("run_packed", layout, nbytes, max_q, max_k, (arena.name, arena.size))
         self._b200_prebuilt = (seqs, layout, nbytes, host, max_q, max_k, arrays["seq_need_compute_logits"].tolist())
+        return self.run(seqs)
+    if method_name == "exit":
+        if self.rank == 0 and self.world_size > 1:
+            self.write_shm("exit")                         # workers first: the tear-down below is collective
+        try:
+            ops.shutdown_collectives()                     # b200_ar_destroy / b200_nvls_destroy, before the group goes
+            return self.exit()
+        finally:
+            release_side_arena(self)
     return _reference_call(self, method_name, *args)
 
 
 def run_packed(self, layout, nbytes, max_q, max_k, payload, _set_context, _reset_context):
     """Worker side of `call("run", seqs)`: same forward as ModelRunner.run on rank > 0 (no sampling there,
-    model_runner.py:631-633), fed from rank 0's packed arena instead of re-deriving it from Sequences."""
+    model_runner.py:631-633), fed from rank 0's packed arena instead of re-deriving it from Sequences.
+    `payload` is the arena itself (bytes) or (name, size) of the side segment that holds it."""
     host = _staging_of(self).get(nbytes)
-    host.numpy()[:nbytes] = np.frombuffer(payload, dtype=np.uint8, count=nbytes)
+    if isinstance(payload, (bytes, bytearray, memoryview)):
+        host.numpy()[:nbytes] = np.frombuffer(payload, dtype=np.uint8, count=nbytes)
+    else:
+        name, _size = payload
+        cur = getattr(self, "_b200_arena", None)
+        if cur is None or cur.name != name:
+            if cur is not None:
+                cur.close()
+            cur = self._b200_arena = _shared_memory(name)
+        host.numpy()[:nbytes] = np.frombuffer(cur.buf, dtype=np.uint8, count=nbytes)
     input_ids, positions = _upload_and_set_context(self, layout, nbytes, host, max_q, max_k, _set_context)
     self.run_model(input_ids, positions)
     _reset_context()

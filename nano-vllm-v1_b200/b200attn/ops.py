@@ -606,3 +606,20 @@ def tp_add_rms_norm(x: torch.Tensor, residual: Optional[torch.Tensor], weight: t
             return _TP_NVLS.all_reduce_add_rms_norm(x, residual, weight, eps)
         flush_pending_all_reduce()
     return rms_norm(x, weight, eps, residual)
+
+
+def shutdown_collectives() -> None:
+    """Tear the peer-memory communicators down (b200_ar_destroy / b200_nvls_destroy) before the reference
+    destroys its process group (ModelRunner.exit, model_runner.py:187-193).  Collective: every rank calls it."""
+    import torch.distributed as dist
+    global _TP_AR, _TP_NVLS, _PENDING
+    _PENDING = None
+    live = [c for c in (_TP_AR, _TP_NVLS) if c not in (None, False)]
+    if not live:
+        return
+    torch.cuda.synchronize()
+    if dist.is_initialized() and dist.get_world_size() > 1:
+        dist.barrier()                              # no rank is still inside a call that reads this rank's buffer
+    for c in live:
+        c.destroy()
+    _TP_AR = _TP_NVLS = None

@@ -187,11 +187,11 @@ __global__ void __launch_bounds__(PF_THREADS, 2) prefill_mma_kernel(const Prefil
 }
 
 int launch_attn_prefill_mma(const PrefillArgs& a, cudaStream_t stream) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce attr_once;                              // opt-in is per device
+    if (attr_once.need()) {
         cudaError_t e = cudaFuncSetAttribute(prefill_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PF_SMEM_BYTES);
         if (e != cudaSuccess) return (int)e;
-        attr_set = true;
+        attr_once.done();
     }
     if (a.batch == 0 || a.total_q == 0 || a.max_q == 0) return 0;
     PrefillParams p;

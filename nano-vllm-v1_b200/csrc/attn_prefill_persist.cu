@@ -505,6 +505,17 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
     }
 }
 
+const CUtensorMap* cached_map(const void* base, uint64_t rows, uint64_t heads, uint64_t row_stride_elems) {
+    static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+    const MapKey key{base, rows, heads, row_stride_elems, current_device()};
+    auto it = cache.find(key);
+    if (it != cache.end()) return &it->second;
+    if (cache.size() >= 4096) cache.clear();                  // bounded; K/V cache maps are re-encoded on demand
+    CUtensorMap m;
+    if (!make_map(&m, base, rows, heads, row_stride_elems)) return nullptr;
+    return &cache.emplace(key, m).first->second;
+}
+
 static long long* g_trace = nullptr;
 static int g_trace_tiles = 0;
 
@@ -515,26 +526,32 @@ int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32
     static const KernelFn kernels[5] = {prefill_persist_kernel<0>, prefill_persist_kernel<1>, prefill_persist_kernel<2>,
                                         prefill_persist_kernel<3>, prefill_persist_kernel<4>};
     static int emu = -1;
-    if (emu < 0) {
+    static PerDeviceOnce once;                                   // the shared-memory opt-in is per device
+    if (once.need()) {
         for (int i = 0; i < 5; ++i) {
             cudaError_t e = cudaFuncSetAttribute(kernels[i], cudaFuncAttributeMaxDynamicSharedMemorySize, PsSmem::ALLOC);
             if (e != cudaSuccess) return (int)e;
         }
+        once.done();
+    }
+    if (emu < 0) {
         const char* env = getenv("B200ATTN_PREFILL_EMU");        // A/B knob; default chosen by measurement
         int v = env ? atoi(env) : PREFILL_EMU_DEFAULT;
         emu = v < 0 ? 0 : (v > 4 ? 4 : v);
     }
-    CUtensorMap mq, mk, mv;
     const bool paged = a.block_tables != nullptr;
-    if (!make_map(&mq, a.q, (uint64_t)a.total_q, (uint64_t)a.Hq, (uint64_t)a.q_token_stride)) return -6;
+    const CUtensorMap* pq = cached_map(a.q, (uint64_t)a.total_q, (uint64_t)a.Hq, (uint64_t)a.q_token_stride);
+    const CUtensorMap *pk, *pv;
     if (paged) {
         const uint64_t rows = (uint64_t)a.num_cache_blocks * B200_PAGE;
-        if (!make_map(&mk, a.k, rows, (uint64_t)a.Hkv, (uint64_t)a.Hkv * B200_HD)) return -6;
-        if (!make_map(&mv, a.v, rows, (uint64_t)a.Hkv, (uint64_t)a.Hkv * B200_HD)) return -6;
+        pk = cached_map(a.k, rows, (uint64_t)a.Hkv, (uint64_t)a.Hkv * B200_HD);
+        pv = cached_map(a.v, rows, (uint64_t)a.Hkv, (uint64_t)a.Hkv * B200_HD);
     } else {
-        if (!make_map(&mk, a.k, (uint64_t)a.total_q, (uint64_t)a.Hkv, (uint64_t)a.k_token_stride)) return -6;
-        if (!make_map(&mv, a.v, (uint64_t)a.total_q, (uint64_t)a.Hkv, (uint64_t)a.v_token_stride)) return -6;
+        pk = cached_map(a.k, (uint64_t)a.total_q, (uint64_t)a.Hkv, (uint64_t)a.k_token_stride);
+        pv = cached_map(a.v, (uint64_t)a.total_q, (uint64_t)a.Hkv, (uint64_t)a.v_token_stride);
     }
+    if (!pq || !pk || !pv) return -6;
+    const CUtensorMap &mq = *pq, &mk = *pk, &mv = *pv;
     PersistParams p;
     p.cu_q = a.cu_q; p.cu_k = a.cu_k; p.block_tables = a.block_tables; p.bt_row_stride = a.bt_row_stride;
     p.out = (__nv_bfloat16*)a.out; p.out_token_stride = a.out_token_stride;
@@ -547,10 +564,10 @@ int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32
     if (grid < 1) grid = 1;
     p.trace = g_trace; p.trace_tiles = g_trace_tiles;
     if (g_trace != nullptr) {
-        static bool trace_attr = false;
-        if (!trace_attr) {
+        static PerDeviceOnce trace_once;
+        if (trace_once.need()) {
             cudaFuncSetAttribute(prefill_persist_kernel<PREFILL_EMU_DEFAULT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, PsSmem::ALLOC);
-            trace_attr = true;
+            trace_once.done();
         }
         prefill_persist_kernel<PREFILL_EMU_DEFAULT, true><<<grid, 384, PsSmem::ALLOC, stream>>>(mq, mk, mv, p);
     } else {

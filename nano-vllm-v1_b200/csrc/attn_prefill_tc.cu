@@ -333,11 +333,11 @@ bool prefill_tc_available() { return get_encode_fn() != nullptr; }
 template <int NQ>
 static int launch_tc(const PrefillArgs& a, cudaStream_t stream) {
     using L = TcSmem<NQ>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce attr_once;                              // opt-in is per device
+    if (attr_once.need()) {
         cudaError_t e = cudaFuncSetAttribute(prefill_tc_kernel<NQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::ALLOC);
         if (e != cudaSuccess) return (int)e;
-        attr_set = true;
+        attr_once.done();
     }
     CUtensorMap mq, mk, mv;
     const bool paged = a.block_tables != nullptr;

@@ -3,6 +3,8 @@
 #pragma once
 #include <cuda.h>
 
+#include <unordered_map>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -153,5 +155,25 @@ static inline bool make_map(CUtensorMap* m, const void* base, uint64_t rows, uin
                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// Tensor maps are a pure function of (base, rows, heads, row stride): encode each one ONCE and reuse it
+// ("encoded on the host once per (cache pointer, Hkv)").  The K/V cache maps of every
+// layer and the handful of q/k/v addresses the caching allocator hands out recur on every step; a step then
+// costs three hash lookups instead of three cuTensorMapEncodeTiled driver calls.  Per process, one Python
+// thread per GPU process (the reference's model), bounded size.
+struct MapKey {
+    const void* base; uint64_t rows, heads, stride; int dev;
+    bool operator==(const MapKey& o) const {
+        return base == o.base && rows == o.rows && heads == o.heads && stride == o.stride && dev == o.dev;
+    }
+};
+struct MapKeyHash {
+    size_t operator()(const MapKey& k) const {
+        uint64_t h = (uint64_t)(uintptr_t)k.base * 0x9E3779B97F4A7C15ull;
+        h ^= (k.rows + 0x632BE59BD9B4E019ull) * 0xC2B2AE3D27D4EB4Full;
+        h ^= (k.heads << 40) ^ (k.stride << 8) ^ (uint64_t)k.dev;
+        return (size_t)(h ^ (h >> 29));
+    }
+};
+const CUtensorMap* cached_map(const void* base, uint64_t rows, uint64_t heads, uint64_t row_stride_elems);   // attn_prefill_persist.cu
 
 }  // namespace b200

@@ -574,3 +574,152 @@ def test_peer_memory_allreduce_world1_and_argument_errors(ops):
     assert not ar.fits(torch.zeros(12, device="cuda").bfloat16())              # not a multiple of 8 elements
     with pytest.raises(RuntimeError):
         ar.all_reduce_(torch.zeros(12, device="cuda").bfloat16())
+    assert ar.status() == 0                                     # no wait timed out
+    ar.destroy()                                                # b200_ar_destroy: frees the buffers, closes IPC maps
+
+
+# ------------------------------------------------------------------ round 2 additions
+@pytest.mark.parametrize("lens", [[1], [1, 1, 1], [1, 5, 1]])
+def test_planned_unpaged_single_token_prompts(ops, lens):
+    """A step of 1-token prompts without a prefix hit: block_tables is None (sum k == sum q, model_runner.py:483)
+    and max_seqlen_q == 1.  The reference calls flash_attn_varlen_func and gets out = v; unpaged 1-token rows are
+    NOT routed to the decode kernel, so the prefill kernel must run them (they used to be left uninitialised)."""
+    Hq, Hkv, D = 16, 8, 128
+    g = torch.Generator().manual_seed(3)
+    T = sum(lens)
+    q = torch.randn(T, Hq, D, generator=g).bfloat16()
+    k = torch.randn(T, Hkv, D, generator=g).bfloat16()
+    v = torch.randn(T, Hkv, D, generator=g).bfloat16()
+    cu = torch.tensor([0] + torch.tensor(lens).cumsum(0).tolist(), dtype=torch.int32)
+    want = oracle.attn_varlen(q, k, v, cu, cu, SCALE)
+    out = torch.full((T, Hq, D), float("nan"), dtype=torch.bfloat16, device="cuda")
+    got = ops.attn_varlen_planned(q.cuda(), k.cuda(), v.cuda(), cu.cuda(), cu.cuda(), max(lens), max(lens), SCALE, out=out)
+    assert torch.isfinite(got.float()).all()
+    assert maxerr(got, want) <= ATOL
+    if max(lens) == 1:                                           # one visible key per row: softmax weight 1 => out == v
+        assert torch.equal(got.cpu(), v.repeat_interleave(Hq // Hkv, dim=1))
+
+
+def test_decode_fused_split_merge_leaves_tickets_zero(ops):
+    """The last split of a (row, kv head) to arrive merges all of them inside the decode launch; the arrival
+    tickets at the head of the workspace re-arm themselves, so every launch (and every CUDA-graph replay)
+    finds zeros.  Ragged rows: some use every split, some fewer, some are padding."""
+    Hq, Hkv = 8, 2
+    lens = [4096, 300, 0, 1, 257, 2000, 16, 4095]
+    c = make_paged_case(77, [1] * len(lens), lens, Hq, Hkv, pad=0, table_width=16)
+    want = oracle.attn_decode(c["q"], c["k_cache"], c["v_cache"], c["context_lens"], c["block_tables"], SCALE)
+    args = [dev(c[n]) for n in ("q", "k_cache", "v_cache", "context_lens", "block_tables")]
+    outs = [ops.attn_decode(*args, SCALE, num_splits=s) for s in (8, 8, 3, 8)]
+    for o in outs:
+        assert maxerr(o, want) <= ATOL
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[3])      # same split count => same bits
+    ws = ops._WS_CACHE[torch.cuda.current_device()]
+    assert int(ws[:64 * 1024].view(torch.int32).abs().sum()) == 0
+
+
+def test_nvls_fused_allreduce_add_rmsnorm_world1(ops):
+    """Single-GPU slice of csrc/allreduce_nvls.cu (multi-GPU parity: bench.py --gpus N `allreduce` leg and
+    tools/ar_check.py): with one rank the sum is the input itself, so the launch must equal b200_rmsnorm with the
+    fused residual add bit for bit -- both forms, repeated calls (slot alternation), CUDA-graph replay; weight None
+    is a plain all-reduce (identity here)."""
+    nv = ops.NvlsAllReduce(None, 1 << 20)
+    g = torch.Generator(device="cuda").manual_seed(5)
+    for T, H in [(1, 1024), (7, 4096), (64, 5120), (33, 1024)]:
+        x = torch.randn(T, H, generator=g, device="cuda").bfloat16()
+        r = torch.randn(T, H, generator=g, device="cuda").bfloat16()
+        w = (1 + 0.1 * torch.randn(H, generator=g, device="cuda")).bfloat16()
+        want_y, want_r = ops.rms_norm(x, w, 1e-6, r.clone())
+        oy, orr = oracle.add_rms_norm(x.cpu(), r.cpu(), w.cpu(), 1e-6)
+        assert _ulp_ok(want_y, oy) and torch.equal(want_r.cpu(), orr)
+        for one_shot in (True, False, None):
+            r2 = r.clone()
+            y, r3 = nv.all_reduce_add_rms_norm(x, r2, w, 1e-6, one_shot=one_shot)
+            assert r3 is r2 and torch.equal(r2, want_r) and torch.equal(y, want_y), (T, H, one_shot)
+        assert torch.equal(nv.all_reduce_add_rms_norm(x, None, None, 0.0), x)          # plain all-reduce
+        assert torch.equal(nv.all_reduce_add_rms_norm(x, None, w, 1e-6), ops.rms_norm(x, w, 1e-6))
+    x = torch.randn(16, 4096, generator=g, device="cuda").bfloat16()
+    w = torch.ones(4096, device="cuda").bfloat16()
+    r0 = torch.randn(16, 4096, generator=g, device="cuda").bfloat16()
+    r, y = r0.clone(), torch.empty_like(x)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        nv.all_reduce_add_rms_norm(x, r, w, 1e-6, out=y)
+    torch.cuda.current_stream().wait_stream(s)
+    gr = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(gr):
+        nv.all_reduce_add_rms_norm(x, r, w, 1e-6, out=y)
+        nv.all_reduce_add_rms_norm(x, r, w, 1e-6, out=y, one_shot=False)
+    r.copy_(r0)
+    gr.replay()
+    rr = r0.clone()
+    ops.rms_norm(x, w, 1e-6, rr)
+    want_y, _ = ops.rms_norm(x, w, 1e-6, rr)
+    torch.cuda.synchronize()
+    assert torch.equal(r, rr) and torch.equal(y, want_y)
+    assert not nv.fits(torch.zeros(1 << 20, 8, device="cuda").bfloat16())                 # 16 MB > 1 MB
+    assert nv.status() == 0
+    nv.destroy()
+
+
+def test_deferred_all_reduce_is_never_left_pending(ops):
+    """Host logic of the fused path on one GPU: outside `deferred_all_reduce` RowParallelLinear's output is reduced
+    at once; nothing stays pending after the context exits."""
+    y = torch.randn(4, 1024, device="cuda").bfloat16()
+    assert ops._PENDING is None
+    with ops.deferred_all_reduce():
+        assert ops._DEFER_DEPTH == 1
+    assert ops._DEFER_DEPTH == 0 and ops._PENDING is None
+    w = torch.ones(1024, device="cuda").bfloat16()
+    out, res = ops.tp_add_rms_norm(y, y.clone(), w, 1e-6)       # no pending sum: plain fused add + RMSNorm
+    assert out.shape == y.shape and res.shape == y.shape
+
+
+def test_cfg4_traced_mixed_batch_vs_oracle(ops):
+    """BASELINE configs[3] at its own traced shape: serving_bench, Qwen3-14B at TP=2 (20 q /
+    4 kv heads per rank, GQA group 5), max-num-batched-tokens 1024: B = 447 rows = 8 x 128-token prompt chunks +
+    439 x 1-token decode rows, Lk 128..228.  Step plan + persistent prefill + routed decode vs the oracle."""
+    Hq, Hkv = 20, 4
+    rnd = torch.Generator().manual_seed(44)
+    dec_k = torch.randint(129, 229, (439,), generator=rnd).tolist()
+    lens_q = [128] * 8 + [1] * 439
+    lens_k = [128] * 8 + dec_k
+    order = torch.randperm(447, generator=rnd).tolist()          # running-first scheduling interleaves them
+    lens_q = [lens_q[i] for i in order]
+    lens_k = [lens_k[i] for i in order]
+    c = make_paged_case(45, lens_q, lens_k, Hq, Hkv, pad=-1)
+    want = oracle.attn_varlen(c["q"], c["k_cache"], c["v_cache"], c["cu_seqlens_q"], c["cu_seqlens_k"], SCALE,
+                              c["block_tables"])
+    cu_q, cu_k = dev(c["cu_seqlens_q"]), dev(c["cu_seqlens_k"])
+    plan = ops.attn_plan(cu_q, cu_k, sum(lens_q), Hq, Hkv, route_decode=True)
+    n_items, n_dec = plan.counts()
+    assert n_dec == 439 and n_items == 8                          # 256-row tiles at an odd GQA group
+    got = torch.full_like(dev(c["q"]), float("nan"))
+    ops.attn_varlen_planned(dev(c["q"]), dev(c["k_cache"]), dev(c["v_cache"]), cu_q, cu_k, 128, max(lens_k), SCALE,
+                            block_table=dev(c["block_tables"]), plan=plan, out=got)
+    assert torch.isfinite(got.float()).all()
+    assert maxerr(got, want) <= ATOL
+
+
+@pytest.mark.parametrize("Hq,Hkv", [(16, 4), (8, 2), (4, 1)])
+def test_decode_full_size_cfg3_tp_shapes(ops, Hq, Hkv):
+    """BASELINE configs[2] at the per-rank head counts of TP=2/4/8, full size (512 seqs x 4096 ctx): sampled rows vs
+    the oracle, automatic split count (what the engine uses) == unsplit within rounding."""
+    B, L, D = 512, 4096, 128
+    nblk = B * (L // 256)
+    g = torch.Generator(device="cuda").manual_seed(10 + Hkv)
+    kc = torch.randn(nblk, 256, Hkv, D, generator=g, device="cuda", dtype=torch.bfloat16)
+    vc = torch.randn(nblk, 256, Hkv, D, generator=g, device="cuda", dtype=torch.bfloat16)
+    q = torch.randn(B, Hq, D, generator=g, device="cuda", dtype=torch.bfloat16)
+    perm = torch.randperm(nblk, generator=torch.Generator().manual_seed(1)).to(torch.int32)
+    bt = perm.view(B, L // 256).cuda()
+    lens = torch.full((B,), L, dtype=torch.int32, device="cuda")
+    out_auto = ops.attn_decode(q, kc, vc, lens, bt, SCALE)
+    out1 = ops.attn_decode(q, kc, vc, lens, bt, SCALE, num_splits=1)
+    assert maxerr(out_auto, out1) <= 4e-3
+    idx = torch.tensor([0, 100, 301, 511])
+    sub_blocks = bt[idx.cuda()].cpu()
+    uniq, inv = torch.unique(sub_blocks, return_inverse=True)
+    want = oracle.attn_decode(q[idx.cuda()].cpu(), kc[uniq.cuda().long()].cpu(), vc[uniq.cuda().long()].cpu(),
+                              lens[idx.cuda()].cpu(), inv.to(torch.int32), SCALE)
+    assert maxerr(out_auto[idx.cuda()], want) <= ATOL

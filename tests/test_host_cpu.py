@@ -185,14 +185,31 @@ def test_tp_control_plane_ships_the_packed_arena(path, monkeypatch):
         else:
             assert got[name].dtype == m[name].dtype and torch.equal(got[name], m[name]), name
 
-    # a step too large for the mailbox falls back to the reference's own message
+    # a step too large for the reference's 1 MiB mailbox travels through a side shared-memory segment: only the
+    # segment's name and the layout go through the mailbox, and the worker ends up with the same Context
     r0.shm.size = 64
+    sent.clear(); ran.clear(); got.clear()
+    try:
+        assert ours.call(r0, "run", seqs, _reference_call=None) == "tokens" and ran == [seqs]
+        method, *args2 = pickle.loads(sent[0])
+        assert method == "run_packed" and isinstance(args2[-1], tuple) and len(sent[0]) < 4096
+        w2 = Worker()
+        w2.forwards = []
+        assert ours.run_packed(w2, *args2, _set_context=None, _reset_context=lambda: None) is None
+        assert len(w2.forwards) == 1 and got["max_q"] == m["max_seqlen_q"]
+        for name in ("input_ids", "positions", "cu_seqlens_q", "cu_seqlens_k", "slot_mapping", "context_lens"):
+            assert torch.equal(got[name], m[name]), name
+        ours.release_side_arena(w2)
+    finally:
+        ours.release_side_arena(r0)
+    # other methods are forwarded untouched; "exit" tells the workers first, tears the peer-memory
+    # communicators down (none here), runs the reference's exit and releases the side segment
     fell = []
-    ours.call(r0, "run", seqs, _reference_call=lambda self, name, *a: fell.append(name))
-    assert fell == ["run"] and len(sent) == 1
-    # other methods are forwarded untouched
+    sent.clear()
+    r0.exit = lambda: fell.append("exit-method")
     ours.call(r0, "exit", _reference_call=lambda self, name, *a: fell.append(name))
-    assert fell == ["run", "exit"]
+    ours.call(r0, "loop", _reference_call=lambda self, name, *a: fell.append(name))
+    assert fell == ["exit-method", "loop"] and pickle.loads(sent[0]) == ["exit"]
 
 
 def test_allreduce_form_policy_and_no_cpu_fallback():

@@ -7,6 +7,10 @@ gets the same harness patches, applied identically to BOTH arms (reference and d
   B200E2E_GREEDY=1            replace Sampler.forward by argmax and record (step, argmax, top-2 logit
                               margin) of every decision per seq_id (the reference's sampler forbids
                               greedy, F12)
+  B200E2E_FP32_LOGITS=1       TP1 only: the LM head multiplies in fp32 (same last-token selection as
+                              embed_head.py:194-204), so top-2 margins are continuous instead of quantised to
+                              bf16 ulps of the logits (one ulp at |logit| in [2,4) is 0.0156: with bf16 logits more
+                              than 1 % of all decisions are EXACT ties in the reference arm itself)
   B200E2E_FORCE_TOKENS=<json> with GREEDY: still record this arm's own argmax, but FEED the token ids
                               of the other arm's run (teacher forcing), so every decision of the two
                               arms is taken on an identical context
@@ -36,16 +40,31 @@ def _patch(module):
     import torch
     if _SEED is not None:
         def seeded_init(model, path):
-            g = torch.Generator(device="cuda").manual_seed(int(_SEED))
+            import torch.distributed as dist
+            rank = dist.get_rank() if dist.is_initialized() else 0
+            # parameters are per-rank shards: every rank draws from its OWN stream (seed + 1000 * rank), the same
+            # in both arms.  One shared stream would make the shards of a vocab- or head-parallel weight identical
+            # copies, i.e. duplicate logits and exact top-2 ties (a degenerate model).
+            g = torch.Generator(device="cuda").manual_seed(int(_SEED) + 1000 * rank)
             with torch.no_grad():
                 for name, p in sorted(model.named_parameters(), key=lambda kv: kv[0]):
                     if name.endswith("norm.weight"):
                         p.fill_(1.0)
                     else:
-                        # parameters are per-rank shards; parity is checked arm-vs-arm at equal TP, so the
-                        # same seeded draw on every rank of both arms suffices
                         p.copy_(torch.randn(p.shape, generator=g, device="cuda", dtype=torch.float32).mul_(0.02).to(p.dtype))
         module.load_model = seeded_init
+    if os.environ.get("B200E2E_FP32_LOGITS") == "1":
+        head = importlib.import_module("nanovllm.layers.embed_head")
+        ctx_mod0 = importlib.import_module("nanovllm.utils.context")
+
+        def fp32_head(self, x):
+            assert self.tp_size == 1, "B200E2E_FP32_LOGITS is a TP1 harness option"
+            context = ctx_mod0.get_context()
+            last = context.cu_seqlens_q[1:] - 1                     # embed_head.py:194-200
+            if context.seq_need_compute_logits.numel():
+                last = last[context.seq_need_compute_logits]
+            return torch.nn.functional.linear(x[last].float(), self.weight.float())
+        head.ParallelLMHead.forward = fp32_head
     if _GREEDY:
         sampler = importlib.import_module("nanovllm.layers.sampler")
         ctx_mod = importlib.import_module("nanovllm.utils.context")

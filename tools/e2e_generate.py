@@ -38,6 +38,8 @@ def launcher(a):
         env["B200E2E_STEP_PROFILE"] = os.path.abspath(a.step_profile)
         if a.kernel_profile:
             env["B200E2E_KERNEL_PROFILE"] = os.path.abspath(a.kernel_profile)
+    if a.fp32_logits:
+        env["B200E2E_FP32_LOGITS"] = "1"
     if a.greedy:
         env["B200E2E_GREEDY"] = "1"
         env["B200E2E_MARGINS_OUT"] = a.out + ".margins"
@@ -135,6 +137,53 @@ def compare(ref_path, our_path, steps, tie_margin):
     return verdict
 
 
+def compare_free(ref_path, our_path, steps, tie_margin):
+    """Greedy parity of two FREE-RUNNING runs (untouched LLM.generate in both arms, argmax sampler).
+    Both arms see identical contexts up to a sequence's first differing token, so there every recorded decision
+    is comparable: the token ids must be identical, and the first difference of a sequence (if any) must sit on a
+    decision whose top-2 logit margin is <= `tie_margin` in BOTH arms (a tie that rounding legitimately flips);
+    everything after it is a different context and is not compared.  The verdict also carries the quantiles of the
+    reference arm's margins over the compared decisions: a caller must reject p1 <= tie_margin (a degenerate
+    model where the tie class could swallow the comparison)."""
+    ref, our = json.load(open(ref_path)), json.load(open(our_path))
+    mref = json.load(open(ref_path + ".margins"))
+    mour = json.load(open(our_path + ".margins"))
+    n = len(ref["token_ids"])
+    compared = identical_seqs = ties = real = 0
+    margins, first_div = [], []
+    for i in range(n):
+        r = {st: (tok, mg) for st, tok, mg in mref[str(i + ref["first_seq_id"])]}
+        o = {st: (tok, mg) for st, tok, mg in mour[str(i + our["first_seq_id"])]}
+        tr, to = ref["token_ids"][i][:steps], our["token_ids"][i][:steps]
+        div = next((t for t in range(min(len(tr), len(to))) if tr[t] != to[t]), None)
+        upto = div if div is not None else min(len(tr), len(to))
+        for t in range(upto):
+            margins.append(r[t][1])
+        compared += upto
+        if div is None:
+            identical_seqs += 1
+            continue
+        compared += 1
+        margins.append(r[div][1])
+        rec = dict(seq=i, step=div, ref_margin=round(r[div][1], 6), our_margin=round(o[div][1], 6))
+        first_div.append(rec)
+        if max(r[div][1], o[div][1]) <= tie_margin:
+            ties += 1
+        else:
+            real += 1
+    margins.sort()
+    q = lambda f: margins[min(int(len(margins) * f), len(margins) - 1)] if margins else None  # noqa: E731
+    first_div.sort(key=lambda d: -max(d["ref_margin"], d["our_margin"]))
+    verdict = dict(sequences=n, steps=steps, decisions_compared=compared, decisions_total=n * steps,
+                   sequences_fully_identical=identical_seqs, first_divergences=len(first_div),
+                   first_divergences_at_tie=ties, first_divergences_for_real=real, tie_margin=tie_margin,
+                   largest_margin_first_divergences=first_div[:8],
+                   ref_margin_quantiles=dict(p0=q(0.0), p0_1=q(0.001), p1=q(0.01), p10=q(0.1), p50=q(0.5)),
+                   teacher_forced=False)
+    print(json.dumps(verdict))
+    return verdict
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--arm", default="dropin", choices=["reference", "dropin", "dropin-attn"])
@@ -152,6 +201,8 @@ def main():
     ap.add_argument("--chunked-prefill", action="store_true")
     ap.add_argument("--enforce-eager", action="store_true")
     ap.add_argument("--greedy", action="store_true")
+    ap.add_argument("--fp32-logits", action="store_true", help="harness (both arms, TP1): LM head in fp32, continuous margins")
+    ap.add_argument("--compare-free", nargs=2, help="free-running greedy parity of two --greedy runs (reference, drop-in)")
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "e2e.json"))
     ap.add_argument("--worker", action="store_true")
@@ -163,6 +214,12 @@ def main():
     ap.add_argument("--kernel-profile", default=None, help="with --step-profile: CUPTI kernel table of 4 decode steps (prefix)")
     ap.add_argument("--step-profile", default=None, help="write per-step phase timings here (perturbs tok/s)")
     a = ap.parse_args()
+    if a.compare_free:
+        v = compare_free(a.compare_free[0], a.compare_free[1], a.steps, a.tie_margin)
+        if a.out:
+            with open(a.out, "w") as f:
+                json.dump(v, f)
+        return 1 if v["first_divergences_for_real"] else 0
     if a.compare:
         v = compare(a.compare[0], a.compare[1], a.steps, a.tie_margin)
         if a.out:
