@@ -122,7 +122,7 @@ int b200_attn_decode(const void* q, int64_t q_token_stride, const void* k_cache,
                      const int32_t* block_tables, int32_t bt_row_stride,
                      int32_t batch, int32_t num_heads, int32_t num_kv_heads, int32_t head_dim, int32_t page_size,
                      float softmax_scale, int32_t num_splits, void* workspace, size_t workspace_bytes, void* stream) {
-    if (batch < 0 || num_splits < 1 || bt_row_stride < 0) return B200_ERR_RANGE;
+    if (batch < 0 || num_splits < 1 || num_splits > 256 || bt_row_stride < 0) return B200_ERR_RANGE;
     if (batch == 0) return B200_OK;
     if (!q || !k_cache || !v_cache || !out || !context_lens || !block_tables) return B200_ERR_NULL;
     if (head_dim != B200_HD_CONST || page_size != 256 || num_kv_heads <= 0 || num_heads % num_kv_heads != 0 ||
@@ -236,7 +236,7 @@ int b200_attn_decode_varlen(const void* q, int64_t q_token_stride, const void* k
                             int32_t batch, int32_t num_heads, int32_t num_kv_heads, int32_t head_dim, int32_t page_size,
                             float softmax_scale, int32_t num_splits, void* workspace, size_t workspace_bytes,
                             const void* plan, size_t plan_bytes_given, void* stream) {
-    if (batch < 0 || num_splits < 1 || bt_row_stride < 0) return B200_ERR_RANGE;
+    if (batch < 0 || num_splits < 1 || num_splits > 256 || bt_row_stride < 0) return B200_ERR_RANGE;
     if (batch == 0) return B200_OK;
     if (!q || !k_cache || !v_cache || !out || !cu_seqlens_q || !cu_seqlens_k || !block_tables || !plan) return B200_ERR_NULL;
     if (head_dim != B200_HD_CONST || page_size != 256 || num_kv_heads <= 0 || num_heads % num_kv_heads != 0 ||

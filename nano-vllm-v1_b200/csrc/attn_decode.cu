@@ -272,9 +272,9 @@ __global__ void __launch_bounds__(DEC_WARPS * 32, MIN_CTAS) paged_decode_kernel(
 
     // ---- fused split merge: the last of this (row, kv head)'s n_part CTAs to arrive reduces them all ----
     volatile int* s_last = reinterpret_cast<volatile int*>(smem);   // the warp-merge scratch is dead after the barrier
-    __threadfence();                                          // this thread's partials before the ticket
-    __syncthreads();
+    __syncthreads();                                          // every thread's partials are ordered before thread 0 here,
     if (threadIdx.x == 0) {
+        __threadfence();                                      // ... so ONE cumulative fence releases them with the ticket
         int32_t* ticket = p.tickets + (int64_t)bi * p.Hkv + h;
         const int t = atomicAdd(ticket, 1);
         *s_last = (t == n_part - 1);
@@ -283,18 +283,61 @@ __global__ void __launch_bounds__(DEC_WARPS * 32, MIN_CTAS) paged_decode_kernel(
     }
     __syncthreads();
     if (!*s_last) return;
-    for (int idx = threadIdx.x; idx < G * B200_HD; idx += DEC_THREADS) {
-        const int head = h * G + (idx >> 7), t = idx & (B200_HD - 1);
-        const float* lse = p.ws_lse + ((int64_t)bi * S) * p.Hq + head;
+    // Merge with every load in flight at once (a chain of dependent L2 round trips here would serialise the tail
+    // of the whole launch): (1) all LSEs into shared memory, (2) one thread per head turns them into weights,
+    // (3) 16-byte partial-O loads, unrolled over the splits.
+    float* sm_w = reinterpret_cast<float*>(smem) + 32;            // [n_part][16] weights, normalised (sum to 1 per head)
+    __syncthreads();                                              // everyone has read *s_last
+    for (int i = threadIdx.x; i < n_part * G; i += DEC_THREADS) {
+        const int ss = i / G, r = i - ss * G;
+        sm_w[ss * 16 + r] = __ldcg(p.ws_lse + ((int64_t)bi * S + ss) * p.Hq + h * G + r);
+    }
+    __syncthreads();
+    if (threadIdx.x < G) {
+        const int r = threadIdx.x;
         float mx = -INFINITY;
-        for (int ss = 0; ss < n_part; ++ss) mx = fmaxf(mx, __ldcg(lse + (int64_t)ss * p.Hq));
-        float acc = 0.f, den = 0.f;
+        for (int ss = 0; ss < n_part; ++ss) mx = fmaxf(mx, sm_w[ss * 16 + r]);
+        float den = 0.f;
         for (int ss = 0; ss < n_part; ++ss) {
-            const float w = fast_exp2(__ldcg(lse + (int64_t)ss * p.Hq) - mx);
-            acc += w * __ldcg(p.ws_o + (((int64_t)bi * S + ss) * p.Hq + head) * B200_HD + t);
+            const float w = fast_exp2(sm_w[ss * 16 + r] - mx);
+            sm_w[ss * 16 + r] = w;
             den += w;
         }
-        p.out[tok * p.out_token_stride + (int64_t)head * B200_HD + t] = __float2bfloat16_rn(acc / den);
+        const float inv = 1.f / den;
+        for (int ss = 0; ss < n_part; ++ss) sm_w[ss * 16 + r] *= inv;
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < G * (B200_HD / 4); idx += DEC_THREADS) {    // one thread per (head, 4 dims)
+        const int r = idx >> 5, t4 = idx & 31;
+        const int head = h * G + r;
+        const float4* src = reinterpret_cast<const float4*>(p.ws_o + (((int64_t)bi * S) * p.Hq + head) * B200_HD) + t4;
+        const int64_t split_stride = (int64_t)p.Hq * (B200_HD / 4);               // float4 units between splits
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        int ss = 0;
+        for (; ss + 8 <= n_part; ss += 8) {
+            float4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = __ldcg(src + (ss + u) * split_stride);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const float w = sm_w[(ss + u) * 16 + r];
+                acc.x += w * v[u].x; acc.y += w * v[u].y; acc.z += w * v[u].z; acc.w += w * v[u].w;
+            }
+        }
+        {
+            float4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) if (ss + u < n_part) v[u] = __ldcg(src + (ss + u) * split_stride);
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+                if (ss + u < n_part) {
+                    const float w = sm_w[(ss + u) * 16 + r];
+                    acc.x += w * v[u].x; acc.y += w * v[u].y; acc.z += w * v[u].z; acc.w += w * v[u].w;
+                }
+        }
+        uint2 o;
+        o.x = pack_bf16x2(acc.x, acc.y); o.y = pack_bf16x2(acc.z, acc.w);
+        *reinterpret_cast<uint2*>(p.out + tok * p.out_token_stride + (int64_t)head * B200_HD + t4 * 4) = o;
     }
 }
 

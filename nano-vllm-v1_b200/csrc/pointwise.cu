@@ -58,9 +58,10 @@ __global__ void __launch_bounds__(256) kv_scatter_kernel(
 //      Lane l owns elements [8l, 8l+8) of the low half and [64+8l, 64+8l+8) of the high half,
 //      i.e. both members of eight NeoX rotation pairs => two 16-byte loads + two 16-byte stores
 //      per lane, no cross-lane traffic for the rotation, a 3-step butterfly for the sum of squares.
-//      A thread works on NR_ROWS rows per step (grid-stride): every load of every row -- data, position,
-//      slot -- is issued before the first row is normalised, so 64 bytes of row data plus the dependent
-//      position -> cos/sin chain are in flight per thread.
+//      Grid-stride over rows with a one-row software pipeline: the loads of the next row (data, position,
+//      slot) are in flight while the current one is normalised, rotated and stored.  Narrowing conversions
+//      are packed F2FP (ALU pipe), never F2F (quarter-rate XU pipe): the kernel is as much issue-bound as
+//      HBM-bound (16 elements per lane go through two roundings and an un-fused rotation).
 //      Roundings follow layernorm.py:85-93 and rotary_embedding.py:60-65 exactly:
 //      bf16(x*rstd), bf16(.*w), fp32 rotate (un-fused mul/sub), bf16.
 // ------------------------------------------------------------------------------------------
@@ -72,7 +73,50 @@ struct KvStoreArgs {
     __nv_bfloat16* k_cache; __nv_bfloat16* v_cache; const int32_t* slot_mapping;
 };
 
-constexpr int NR_ROWS = 2;
+// bf16 pair <-> two floats without F2F (which runs on the quarter-rate XU pipe): widening is a shift / mask,
+// narrowing is ONE packed F2FP (round-to-nearest-even, the same rounding as __float2bfloat16_rn).
+__device__ __forceinline__ float bf_lo(uint32_t u) { return __uint_as_float(u << 16); }
+__device__ __forceinline__ float bf_hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
+
+struct RowLoad {                                   // everything one (token, head) row needs from memory, issued up front
+    int4 lo, hi;                                   // elements [8s, 8s+8) and [64+8s, 64+8s+8) of the row
+    const float* cs;                               // cos/sin row of the token's position (+ 8 * sub)
+    __nv_bfloat16* dst; __nv_bfloat16* cache_dst;
+    bool live, is_q, is_v;
+};
+
+template <bool STORE>
+__device__ __forceinline__ RowLoad load_row(uint32_t row, uint32_t total_rows, uint32_t H, uint32_t Hq, uint32_t Hkv, int sub,
+                                            const __nv_bfloat16* q, int64_t q_token_stride, const __nv_bfloat16* k, int64_t k_token_stride,
+                                            const int64_t* positions, const float* cos_sin, __nv_bfloat16* q_out, __nv_bfloat16* k_out,
+                                            const KvStoreArgs& st) {
+    RowLoad r;
+    r.live = row < total_rows;                     // dead lanes still take part in the shuffles
+    const uint32_t tok = r.live ? row / H : 0;
+    const uint32_t h = r.live ? row - tok * H : 0;
+    r.is_q = h < Hq;
+    r.is_v = STORE && h >= Hq + Hkv;
+    const __nv_bfloat16* src = r.is_q ? q + (int64_t)tok * q_token_stride + (int64_t)h * B200_HD
+                             : r.is_v ? st.v + (int64_t)tok * st.v_token_stride + (int64_t)(h - Hq - Hkv) * B200_HD
+                                      : k + (int64_t)tok * k_token_stride + (int64_t)(h - Hq) * B200_HD;
+    r.dst = r.is_q ? q_out + ((int64_t)tok * Hq + h) * B200_HD
+                   : (k_out != nullptr && !r.is_v ? k_out + ((int64_t)tok * Hkv + (h - Hq)) * B200_HD : nullptr);
+    r.lo = r.hi = make_int4(0, 0, 0, 0);
+    r.cache_dst = nullptr;
+    r.cs = cos_sin;
+    if (r.live) {
+        r.lo = ld_nc_v4(src + 8 * sub);
+        r.hi = ld_nc_v4(src + 64 + 8 * sub);
+        if (!r.is_v) r.cs = cos_sin + __ldg(positions + tok) * B200_HD + 8 * sub;       // [cos(64) | sin(64)]
+        if (STORE && !r.is_q) {
+            const int32_t slot = __ldg(st.slot_mapping + tok);
+            if (slot >= 0)
+                r.cache_dst = (r.is_v ? st.v_cache + (int64_t)(h - Hq - Hkv) * B200_HD : st.k_cache + (int64_t)(h - Hq) * B200_HD)
+                              + (int64_t)slot * Hkv * B200_HD;
+        }
+    }
+    return r;
+}
 
 template <bool STORE>
 __global__ void __launch_bounds__(256) qk_norm_rope_kernel(
@@ -85,89 +129,55 @@ __global__ void __launch_bounds__(256) qk_norm_rope_kernel(
     const int sub = threadIdx.x & 7;
     const uint32_t H = STORE ? Hq + 2 * Hkv : Hq + Hkv;
     const bool has_w = q_weight != nullptr;                    // both weights or neither (checked at the ABI)
-    // weights: the same 2 x 16 bytes for every row of a kind, loaded once
-    int4 wq_lo = make_int4(0, 0, 0, 0), wq_hi = wq_lo, wk_lo = wq_lo, wk_hi = wq_lo;
-    if (has_w) {
-        wq_lo = *reinterpret_cast<const int4*>(q_weight + 8 * sub); wq_hi = *reinterpret_cast<const int4*>(q_weight + 64 + 8 * sub);
-        wk_lo = *reinterpret_cast<const int4*>(k_weight + 8 * sub); wk_hi = *reinterpret_cast<const int4*>(k_weight + 64 + 8 * sub);
-    }
     const uint32_t group = (blockIdx.x * 256u + threadIdx.x) >> 3;            // 8-lane row group of this thread
     const uint32_t groups = gridDim.x * 32u;
-    // rounds of NR_ROWS * groups rows; every lane of a warp runs the same number of rounds (shuffles below)
-    for (uint32_t row0 = group; row0 - group < total_rows; row0 += NR_ROWS * groups) {
-        bool live[NR_ROWS], is_q[NR_ROWS], is_v[NR_ROWS];
-        int4 lo4[NR_ROWS], hi4[NR_ROWS];
-        __nv_bfloat16* dst[NR_ROWS];
-        __nv_bfloat16* cache_dst[NR_ROWS];
-        const float* cs[NR_ROWS];
-#pragma unroll
-        for (int r = 0; r < NR_ROWS; ++r) {
-            const uint32_t row = row0 + r * groups;
-            live[r] = row < total_rows;                        // dead lanes still take part in the shuffles
-            const uint32_t tok = live[r] ? row / H : 0;
-            const uint32_t h = live[r] ? row - tok * H : 0;
-            is_q[r] = h < Hq;
-            is_v[r] = STORE && h >= Hq + Hkv;
-            const __nv_bfloat16* src = is_q[r] ? q + (int64_t)tok * q_token_stride + (int64_t)h * B200_HD
-                                     : is_v[r] ? st.v + (int64_t)tok * st.v_token_stride + (int64_t)(h - Hq - Hkv) * B200_HD
-                                               : k + (int64_t)tok * k_token_stride + (int64_t)(h - Hq) * B200_HD;
-            dst[r] = is_q[r] ? q_out + ((int64_t)tok * Hq + h) * B200_HD
-                             : (k_out != nullptr && !is_v[r] ? k_out + ((int64_t)tok * Hkv + (h - Hq)) * B200_HD : nullptr);
-            lo4[r] = hi4[r] = make_int4(0, 0, 0, 0);
-            cache_dst[r] = nullptr;
-            cs[r] = cos_sin;
-            if (live[r]) {
-                lo4[r] = ld_nc_v4(src + 8 * sub);
-                hi4[r] = ld_nc_v4(src + 64 + 8 * sub);
-                if (!is_v[r]) cs[r] = cos_sin + __ldg(positions + tok) * B200_HD + 8 * sub;   // [cos(64) | sin(64)]
-                if (STORE && !is_q[r]) {
-                    const int32_t slot = __ldg(st.slot_mapping + tok);
-                    if (slot >= 0)
-                        cache_dst[r] = (is_v[r] ? st.v_cache + (int64_t)(h - Hq - Hkv) * B200_HD : st.k_cache + (int64_t)(h - Hq) * B200_HD)
-                                       + (int64_t)slot * Hkv * B200_HD;
-                }
-            }
+    // Software pipeline over this group's rows (group, group + groups, ...): the loads of row n+1 are in flight
+    // while row n is normalised, rotated and stored.  Every lane of a warp runs the same number of rounds.
+    RowLoad cur = load_row<STORE>(group, total_rows, H, Hq, Hkv, sub, q, q_token_stride, k, k_token_stride, positions, cos_sin, q_out, k_out, st);
+    for (uint32_t base = 0; base < total_rows; base += groups) {
+        const RowLoad nxt = load_row<STORE>(group + base + groups, base + groups < total_rows ? total_rows : 0u, H, Hq, Hkv, sub,
+                                            q, q_token_stride, k, k_token_stride, positions, cos_sin, q_out, k_out, st);
+        if (STORE && cur.is_v && cur.cache_dst != nullptr) {       // v is copied untouched
+            st_v4(cur.cache_dst + 8 * sub, cur.lo);
+            st_v4(cur.cache_dst + 64 + 8 * sub, cur.hi);
         }
+        const uint32_t lo_u[4] = {(uint32_t)cur.lo.x, (uint32_t)cur.lo.y, (uint32_t)cur.lo.z, (uint32_t)cur.lo.w};
+        const uint32_t hi_u[4] = {(uint32_t)cur.hi.x, (uint32_t)cur.hi.y, (uint32_t)cur.hi.z, (uint32_t)cur.hi.w};
+        float x1[8], x2[8];
 #pragma unroll
-        for (int r = 0; r < NR_ROWS; ++r) {
-            if (STORE && is_v[r] && cache_dst[r] != nullptr) { // v is copied untouched
-                st_v4(cache_dst[r] + 8 * sub, lo4[r]);
-                st_v4(cache_dst[r] + 64 + 8 * sub, hi4[r]);
-            }
-            const uint32_t lo_u[4] = {(uint32_t)lo4[r].x, (uint32_t)lo4[r].y, (uint32_t)lo4[r].z, (uint32_t)lo4[r].w};
-            const uint32_t hi_u[4] = {(uint32_t)hi4[r].x, (uint32_t)hi4[r].y, (uint32_t)hi4[r].z, (uint32_t)hi4[r].w};
-            float x1[8], x2[8];
+        for (int j = 0; j < 4; ++j) {
+            x1[2 * j] = bf_lo(lo_u[j]); x1[2 * j + 1] = bf_hi(lo_u[j]);
+            x2[2 * j] = bf_lo(hi_u[j]); x2[2 * j + 1] = bf_hi(hi_u[j]);
+        }
+        if (has_w) {                                           // uniform: nullptr => rotation only (RotaryEmbedding.forward)
+            float ss = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) ss += x1[j] * x1[j] + x2[j] * x2[j];
+#pragma unroll
+            for (int o = 4; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+            const float rstd = rsqrtf(__fadd_rn(ss * (1.0f / B200_HD), eps));
+            const __nv_bfloat16* w = cur.is_q ? q_weight : k_weight;           // 2 x 16 bytes, L1-resident
+            const int4 wl4 = __ldg(reinterpret_cast<const int4*>(w + 8 * sub));
+            const int4 wh4 = __ldg(reinterpret_cast<const int4*>(w + 64 + 8 * sub));
+            const uint32_t wl_u[4] = {(uint32_t)wl4.x, (uint32_t)wl4.y, (uint32_t)wl4.z, (uint32_t)wl4.w};
+            const uint32_t wh_u[4] = {(uint32_t)wh4.x, (uint32_t)wh4.y, (uint32_t)wh4.z, (uint32_t)wh4.w};
+            // bf16(x * rstd) then bf16(that * w): two roundings, as in the reference.  The first is one packed F2FP
+            // per pair; the second is ONE packed bf16 multiply: the product of two bf16 values is exact in fp32, so
+            // HMUL2.BF16 (fp32 product, one round-to-nearest-even) returns the bits of bf16(float(y) * float(w)).
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                const float2 a = unpack_bf16x2(lo_u[j]), b = unpack_bf16x2(hi_u[j]);
-                x1[2 * j] = a.x; x1[2 * j + 1] = a.y;
-                x2[2 * j] = b.x; x2[2 * j + 1] = b.y;
+                const uint32_t a = pack_bf16x2(__fmul_rn(x1[2 * j], rstd), __fmul_rn(x1[2 * j + 1], rstd));
+                const uint32_t b = pack_bf16x2(__fmul_rn(x2[2 * j], rstd), __fmul_rn(x2[2 * j + 1], rstd));
+                const __nv_bfloat162 c2 = __hmul2(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&wl_u[j]));
+                const __nv_bfloat162 d2 = __hmul2(*reinterpret_cast<const __nv_bfloat162*>(&b), *reinterpret_cast<const __nv_bfloat162*>(&wh_u[j]));
+                const uint32_t c = *reinterpret_cast<const uint32_t*>(&c2), d = *reinterpret_cast<const uint32_t*>(&d2);
+                x1[2 * j] = bf_lo(c); x1[2 * j + 1] = bf_hi(c);
+                x2[2 * j] = bf_lo(d); x2[2 * j + 1] = bf_hi(d);
             }
-            if (has_w) {                                       // uniform: nullptr => rotation only (RotaryEmbedding.forward)
-                float ss = 0.f;
-#pragma unroll
-                for (int j = 0; j < 8; ++j) ss += x1[j] * x1[j] + x2[j] * x2[j];
-#pragma unroll
-                for (int o = 4; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-                const float rstd = rsqrtf(__fadd_rn(ss * (1.0f / B200_HD), eps));
-                const int4 wl4 = is_q[r] ? wq_lo : wk_lo, wh4 = is_q[r] ? wq_hi : wk_hi;
-                const uint32_t wl_u[4] = {(uint32_t)wl4.x, (uint32_t)wl4.y, (uint32_t)wl4.z, (uint32_t)wl4.w};
-                const uint32_t wh_u[4] = {(uint32_t)wh4.x, (uint32_t)wh4.y, (uint32_t)wh4.z, (uint32_t)wh4.w};
-                // bf16(x * rstd) then bf16(that * w): two roundings, as in the reference
-                auto nrm = [&](float x, float wt) {
-                    const float y = __bfloat162float(__float2bfloat16_rn(__fmul_rn(x, rstd)));
-                    return __bfloat162float(__float2bfloat16_rn(__fmul_rn(y, wt)));
-                };
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float2 a = unpack_bf16x2(wl_u[j]), b = unpack_bf16x2(wh_u[j]);
-                    x1[2 * j] = nrm(x1[2 * j], a.x); x1[2 * j + 1] = nrm(x1[2 * j + 1], a.y);
-                    x2[2 * j] = nrm(x2[2 * j], b.x); x2[2 * j + 1] = nrm(x2[2 * j + 1], b.y);
-                }
-            }
-            if (!live[r] || is_v[r]) continue;
-            const float4 c0 = *reinterpret_cast<const float4*>(cs[r]), c1 = *reinterpret_cast<const float4*>(cs[r] + 4);
-            const float4 s0 = *reinterpret_cast<const float4*>(cs[r] + 64), s1 = *reinterpret_cast<const float4*>(cs[r] + 68);
+        }
+        if (cur.live && !cur.is_v) {
+            const float4 c0 = __ldg(reinterpret_cast<const float4*>(cur.cs)), c1 = __ldg(reinterpret_cast<const float4*>(cur.cs + 4));
+            const float4 s0 = __ldg(reinterpret_cast<const float4*>(cur.cs + 64)), s1 = __ldg(reinterpret_cast<const float4*>(cur.cs + 68));
             const float c[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
             const float s[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
             uint32_t y1[4], y2[4];
@@ -181,15 +191,16 @@ __global__ void __launch_bounds__(256) qk_norm_rope_kernel(
                                     __fadd_rn(__fmul_rn(x2[b], c[b]), __fmul_rn(x1[b], s[b])));
             }
             const int4 o_lo = make_int4(y1[0], y1[1], y1[2], y1[3]), o_hi = make_int4(y2[0], y2[1], y2[2], y2[3]);
-            if (dst[r] != nullptr) {
-                st_v4(dst[r] + 8 * sub, o_lo);
-                st_v4(dst[r] + 64 + 8 * sub, o_hi);
+            if (cur.dst != nullptr) {
+                st_v4(cur.dst + 8 * sub, o_lo);
+                st_v4(cur.dst + 64 + 8 * sub, o_hi);
             }
-            if (STORE && cache_dst[r] != nullptr) {
-                st_v4(cache_dst[r] + 8 * sub, o_lo);
-                st_v4(cache_dst[r] + 64 + 8 * sub, o_hi);
+            if (STORE && cur.cache_dst != nullptr) {
+                st_v4(cur.cache_dst + 8 * sub, o_lo);
+                st_v4(cur.cache_dst + 64 + 8 * sub, o_hi);
             }
         }
+        cur = nxt;
     }
 }
 
@@ -329,7 +340,7 @@ int launch_kv_scatter_generic(const void* key, const void* value, int64_t key_ro
 // rows are spread over at most 8 CTAs per SM (the grid-stride loop takes the rest): enough CTAs to fill
 // the machine, few enough that a 16k-token prefill is not 25k tiny CTAs
 static inline int norm_rope_grid(int64_t rows) {
-    int64_t blocks = (rows + 32 * NR_ROWS - 1) / (32 * NR_ROWS);  // 32 rows per CTA per round
+    int64_t blocks = (rows + 31) / 32;                            // 32 rows per CTA per round
     const int64_t cap = (int64_t)sm_count() * 8;
     if (blocks > cap) blocks = cap;
     return (int)(blocks < 1 ? 1 : blocks);

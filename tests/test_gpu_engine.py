@@ -1,19 +1,35 @@
 """Engine-level parity on a B200 (SURVEY rows a11, a13 and the north_star greedy rule): the reference's UNTOUCHED
 `LLM.generate` -- v1 scheduler, BlockManager, chunked prefill, `allocate_kv_cache`, `capture_cudagraph`,
-CUDA-graph replay of decode -- is run twice in subprocesses on the same seeded random-init synthetic Qwen3:
+CUDA-graph replay of decode -- is run in subprocesses on the same seeded random-init synthetic Qwen3 (4 layers of the
+0.6B shape, 32 prompts x 128 tokens, 64 decode steps, max_num_batched_tokens 1000 so prompts are chunked and
+steps mix prefill chunks with decode rows):
 
   reference arm : the unmodified offline install `baseline/_ref` (Triton store_kvcache + flash-attn 2.8.3 + inductor)
   drop-in arm   : the same install with `b200attn.install.install()` applied by the import hook (every sm_100a kernel
-                  of this repo on the path, ModelRunner hooks included)
+                  of this repo on the path, ModelRunner hooks included), once free-running and once teacher-forced
+                  (fed the reference arm's tokens, so all 2048 decisions of both arms are taken on identical contexts)
 
 Both arms get the same harness patches (tools/e2e/sitecustomize.py): seeded N(0, 0.02) weights (per-rank streams), an
-arg-max sampler that records top-2 logit margins (the reference's sampler forbids greedy) and an fp32 LM
-head, so margins are continuous instead of quantised to bf16 ulps of the logits.
+arg-max sampler that records the top-1 logit and the top-2 margin (the reference's sampler forbids greedy)
+and an fp32 LM head, so margins are continuous instead of quantised to bf16 ulps of the logits.
 
-Rule asserted (tools/e2e_generate.py compare_free): token ids identical over 64 steps; a sequence may leave the
-reference trajectory only at a decision whose top-2 margin is <= TIE_MARGIN in BOTH arms, and the reference arm's own
-1 % margin quantile must lie ABOVE TIE_MARGIN -- so the tie class can excuse at most ~1 % of the decisions and a
-degenerate model (duplicate logits, exact ties) fails the test instead of passing it vacuously.
+What can and cannot be asserted.  The logits of this model are ~N(0, 0.64^2) over 151,936 tokens; the gap between the
+two largest falls below g with probability ~ 4.9 g / sigma, so among 2048 decisions the smallest margins are ~1e-5 and
+the 1 % quantile is ~3e-3 -- whatever the seed, and ~12 % of all margins are below 0.03.  Two correct bf16
+implementations do not produce the same bits: measured on a B200 (profiles/r2_engine_parity_calibration.json) the
+top-1 logit of the two arms differs by 0.0037 (median) to 0.0195 (max of 2048) on IDENTICAL contexts -- 0.6 % to 3 %
+of sigma, the size of one bf16 ulp of the final hidden state -- with 2 layers as with 4.  A decision whose margin is
+inside that noise is a coin flip for ANY pair of implementations (flash-attn 2 vs 3 included), so "identical over 64
+steps" is asserted outside a tie class, and the tie class is kept honest by four guards instead of by the
+unattainable "1 % margin quantile above the noise":
+
+  * LOGIT parity, all decisions, teacher-forced: |top-1 logit difference| <= LOGIT_TOL = 0.03 (an attention bug --
+    wrong page, mask, scale, stale cache row -- moves logits by O(sigma) = 0.6);
+  * TOKEN parity, all decisions, teacher-forced: identical wherever either arm's margin exceeds TIE_MARGIN = 0.03;
+    at most 3 % of the decisions may differ at all;
+  * the model is not degenerate: no exact ties (p0 > 0), median margin > 3 x TIE_MARGIN, tie class <= 20 %;
+  * free-running: a sequence leaves the reference trajectory only at a decision inside the tie class, and at least
+    half of the sequences never leave it.
 """
 import json
 import os
@@ -26,15 +42,14 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF = os.path.join(ROOT, "baseline", "_ref", "nanovllm")
 TOOL = os.path.join(ROOT, "tools", "e2e_generate.py")
 
-# fp32 logits of this model have sigma ~ 0.64 (N(0, 0.02) LM head on a unit-RMS hidden state of 1024 dims); the gap
-# between the two largest of 151,936 such logits falls below g with probability ~ 4.9 g / sigma, so the 1 % quantile
-# sits near 1.3e-3.  Two arms that differ by bf16 roundings inside 4 layers move a logit by a few 1e-4.
-TIE_MARGIN = 1.0e-3
+LOGIT_TOL = 0.03          # max |top-1 logit(reference) - top-1 logit(drop-in)| on identical contexts (measured max 0.0195)
+TIE_MARGIN = 0.03         # a decision with a top-2 margin below this in BOTH arms may legitimately flip (measured max 0.0157)
 STEPS = 64
+SEQS = 32
 
 
 def _run_arm(arm, out, extra=()):
-    cmd = [sys.executable, TOOL, "--arm", arm, "--size", "0.6b", "--layers", "4", "--num-seqs", "32", "--in-len", "128",
+    cmd = [sys.executable, TOOL, "--arm", arm, "--size", "0.6b", "--layers", "4", "--num-seqs", str(SEQS), "--in-len", "128",
            "--out-len", str(STEPS), "--chunked-prefill", "--max-model-len", "1024", "--max-num-batched-tokens", "1000",
            "--gpu-memory-utilization", "0.3", "--greedy", "--fp32-logits", "--out", out, *extra]
     env = dict(os.environ)
@@ -46,30 +61,42 @@ def _run_arm(arm, out, extra=()):
 
 
 @pytest.mark.gpu
-@pytest.mark.timeout(3600)
 def test_llm_generate_greedy_tokens_identical_to_reference_arm(tmp_path):
     if not os.path.isdir(REF):
         pytest.skip("baseline/_ref (offline install of the reference, __graft_entry__.build()) is not in this tree")
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     import e2e_generate
 
-    ref = _run_arm("reference", str(tmp_path / "ref.json"))
-    our = _run_arm("dropin", str(tmp_path / "our.json"))
-    assert ref["dropin_installed"] is False and our["dropin_installed"] is True
+    ref_p, our_p, tf_p = (str(tmp_path / n) for n in ("ref.json", "our.json", "tf.json"))
+    ref = _run_arm("reference", ref_p)
+    our = _run_arm("dropin", our_p)
+    forced = _run_arm("dropin", tf_p, ("--force-tokens", ref_p))
+    assert ref["dropin_installed"] is False and our["dropin_installed"] is True and forced["dropin_installed"] is True
     assert not ref["enforce_eager"] and not our["enforce_eager"] and our["chunked_prefill"]      # graphs on, chunked
-    assert len(ref["token_ids"]) == len(our["token_ids"]) == 32
-    assert all(len(t) == STEPS for t in ref["token_ids"]) and all(len(t) == STEPS for t in our["token_ids"])
+    for rec in (ref, our, forced):
+        assert len(rec["token_ids"]) == SEQS and all(len(t) == STEPS for t in rec["token_ids"])
+    assert forced["token_ids"] == ref["token_ids"]                 # teacher forcing fed the reference's tokens
 
-    v = e2e_generate.compare_free(str(tmp_path / "ref.json"), str(tmp_path / "our.json"), STEPS, TIE_MARGIN)
+    tf = e2e_generate.compare(ref_p, tf_p, STEPS, TIE_MARGIN)
+    free = e2e_generate.compare_free(ref_p, our_p, STEPS, TIE_MARGIN)
+    with open(ref_p + ".margins") as f:
+        margins = sorted(rec[2] for recs in json.load(f).values() for rec in recs if rec[0] < STEPS)
+    tie_class = sum(1 for m in margins if m <= TIE_MARGIN) / len(margins)
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     with open(os.path.join(ROOT, "gpurun_out", "engine_greedy_parity.json"), "w") as f:
-        json.dump(dict(v, ref_tok_per_s=ref["tok_per_s"], our_tok_per_s=our["tok_per_s"]), f)
-    q = v["ref_margin_quantiles"]
-    # the model is not degenerate: no exact ties, and at most ~1 % of the decisions can fall in the tie class
-    assert q["p0"] > 0.0, v
-    assert q["p1"] > TIE_MARGIN, f"reference arm's own margins are too small for a meaningful comparison: {v}"
-    # no sequence leaves the reference trajectory at a decision that either arm made with a clear margin
-    assert v["first_divergences_for_real"] == 0, v
-    # and the comparison is not vacuous: most decisions were taken on identical contexts and were identical
-    assert v["decisions_compared"] >= 0.8 * v["decisions_total"], v
-    assert v["sequences_fully_identical"] >= 0.6 * v["sequences"], v
+        json.dump(dict(teacher_forced=tf, free_running=free, tie_class_fraction=tie_class, logit_tol=LOGIT_TOL,
+                       ref_tok_per_s=ref["tok_per_s"], our_tok_per_s=our["tok_per_s"]), f)
+
+    # (1) logits agree on every decision taken on an identical context
+    noise = tf["top1_logit_abs_diff"]
+    assert tf["decisions"] == SEQS * STEPS and noise["max"] is not None and noise["max"] <= LOGIT_TOL, tf
+    # (2) tokens identical outside the tie class, and almost everywhere
+    assert tf["differ_for_real"] == 0, tf
+    assert tf["identical"] >= 0.97 * tf["decisions"], tf
+    # (3) the model is not degenerate and the tie class is small
+    q = tf["ref_margin_quantiles"]
+    assert q["p0"] > 0.0 and q["p50"] > 3 * TIE_MARGIN and tie_class <= 0.20, (q, tie_class)
+    # (4) free-running generate: trajectories identical up to a tie, most of them to the end
+    assert free["first_divergences_for_real"] == 0, free
+    assert free["sequences_fully_identical"] >= 0.5 * SEQS, free
+    assert free["decisions_compared"] >= 0.6 * free["decisions_total"], free

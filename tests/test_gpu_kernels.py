@@ -619,9 +619,10 @@ def test_decode_fused_split_merge_leaves_tickets_zero(ops):
 
 def test_nvls_fused_allreduce_add_rmsnorm_world1(ops):
     """Single-GPU slice of csrc/allreduce_nvls.cu (multi-GPU parity: bench.py --gpus N `allreduce` leg and
-    tools/ar_check.py): with one rank the sum is the input itself, so the launch must equal b200_rmsnorm with the
-    fused residual add bit for bit -- both forms, repeated calls (slot alternation), CUDA-graph replay; weight None
-    is a plain all-reduce (identity here)."""
+    tools/ar_check.py): with one rank the sum is the input itself, so the launch must give the residual of
+    add_rms_forward bit for bit and its normed output within 1 bf16 ulp of the oracle (the sum of squares is
+    accumulated in a different order than in b200_rmsnorm, so the two kernels may differ in a last bit) -- both
+    forms, repeated calls (slot alternation), CUDA-graph replay; weight None is a plain all-reduce (identity here)."""
     nv = ops.NvlsAllReduce(None, 1 << 20)
     g = torch.Generator(device="cuda").manual_seed(5)
     for T, H in [(1, 1024), (7, 4096), (64, 5120), (33, 1024)]:
@@ -634,9 +635,10 @@ def test_nvls_fused_allreduce_add_rmsnorm_world1(ops):
         for one_shot in (True, False, None):
             r2 = r.clone()
             y, r3 = nv.all_reduce_add_rms_norm(x, r2, w, 1e-6, one_shot=one_shot)
-            assert r3 is r2 and torch.equal(r2, want_r) and torch.equal(y, want_y), (T, H, one_shot)
+            assert r3 is r2 and torch.equal(r2, want_r) and _ulp_ok(y, oy), (T, H, one_shot)
+            assert (y == want_y).float().mean() > 0.99, (T, H, one_shot)
         assert torch.equal(nv.all_reduce_add_rms_norm(x, None, None, 0.0), x)          # plain all-reduce
-        assert torch.equal(nv.all_reduce_add_rms_norm(x, None, w, 1e-6), ops.rms_norm(x, w, 1e-6))
+        assert _ulp_ok(nv.all_reduce_add_rms_norm(x, None, w, 1e-6), oracle.rms_norm(x.cpu(), w.cpu(), 1e-6))
     x = torch.randn(16, 4096, generator=g, device="cuda").bfloat16()
     w = torch.ones(4096, device="cuda").bfloat16()
     r0 = torch.randn(16, 4096, generator=g, device="cuda").bfloat16()
@@ -656,7 +658,7 @@ def test_nvls_fused_allreduce_add_rmsnorm_world1(ops):
     ops.rms_norm(x, w, 1e-6, rr)
     want_y, _ = ops.rms_norm(x, w, 1e-6, rr)
     torch.cuda.synchronize()
-    assert torch.equal(r, rr) and torch.equal(y, want_y)
+    assert torch.equal(r, rr) and (y == want_y).float().mean() > 0.99 and _ulp_ok(y, want_y.cpu(), 2)
     assert not nv.fits(torch.zeros(1 << 20, 8, device="cuda").bfloat16())                 # 16 MB > 1 MB
     assert nv.status() == 0
     nv.destroy()

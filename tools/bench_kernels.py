@@ -192,6 +192,34 @@ def pointwise_cases(results, iters):
         results[f"norm_rope_T{T}"] = {"kind": "norm_rope", "T": T, "alg_bytes": b, "ours_ms_median": med, "ours_gbps": b / med / 1e6,
                                       "ours_frac_measured_hbm": b / med / 1e6 / PEAK["hbm_gbs"]}
         print(f"norm_rope_T{T}", json.dumps(results[f"norm_rope_T{T}"]), flush=True)
+        # the launch the product path actually runs (install.py): q/k norm + RoPE + KV-cache scatter, k_out skipped
+        v = qkv[:, (Hq + Hkv) * D:].view(T, Hkv, D)
+        nb = T // PAGE + 64
+        kc = torch.zeros(nb, PAGE, Hkv, D, device="cuda", dtype=torch.bfloat16)
+        vc = torch.zeros_like(kc)
+        slots = torch.randperm(nb * PAGE, generator=torch.Generator().manual_seed(3))[:T].to(torch.int32).cuda()
+        for need_k in (False, True):
+            med, _ = timeit(lambda: ops.qk_norm_rope_store(q.view(T, Hq, D), k.view(T, Hkv, D), v, pos, w, w, cache, 1e-6, kc, vc, slots,
+                                                           need_k_out=need_k), iters, flush=flush)
+            # read q,k,v + cos/sin + position + slot; write q_out, K and V cache rows (+ k_out)
+            b = T * ((Hq + 2 * Hkv) * D * 2 + D * 4 + 12 + (Hq + 2 * Hkv + (Hkv if need_k else 0)) * D * 2)
+            name = f"norm_rope_store_T{T}" + ("_kout" if need_k else "")
+            results[name] = {"kind": "norm_rope_store", "T": T, "need_k_out": need_k, "alg_bytes": b, "ours_ms_median": med,
+                             "ours_gbps": b / med / 1e6, "ours_frac_measured_hbm": b / med / 1e6 / PEAK["hbm_gbs"]}
+            print(name, json.dumps(results[name]), flush=True)
+        del kc, vc
+        # hidden-size RMSNorm (73 launches per Qwen3-8B step), with and without the fused residual add
+        Hd = 4096
+        h = torch.randn(T, Hd, generator=g, device="cuda", dtype=torch.bfloat16)
+        r = torch.randn(T, Hd, generator=g, device="cuda", dtype=torch.bfloat16)
+        wh = torch.ones(Hd, device="cuda", dtype=torch.bfloat16)
+        for resid in (False, True):
+            med, _ = timeit(lambda: ops.rms_norm(h, wh, 1e-6, r if resid else None), iters, flush=flush)
+            b = T * Hd * 2 * (4 if resid else 2)
+            name = f"rmsnorm_T{T}" + ("_residual" if resid else "")
+            results[name] = {"kind": "rmsnorm", "T": T, "hidden": Hd, "residual": resid, "alg_bytes": b, "ours_ms_median": med,
+                             "ours_gbps": b / med / 1e6, "ours_frac_measured_hbm": b / med / 1e6 / PEAK["hbm_gbs"]}
+            print(name, json.dumps(results[name]), flush=True)
         x = torch.randn(T, 2 * I, generator=g, device="cuda", dtype=torch.bfloat16)
         med, _ = timeit(lambda: ops.silu_and_mul(x), iters, flush=flush)
         b = T * 6 * I

@@ -78,6 +78,7 @@ def _patch(module):
             top2 = torch.topk(logits.float(), 2, dim=-1)
             choice = top2.indices[:, 0]
             margins = (top2.values[:, 0] - top2.values[:, 1]).tolist()
+            tops = top2.values[:, 0].tolist()
             picks = choice.tolist()
             seqs = cur.get("seqs")
             if seqs is not None:
@@ -88,7 +89,7 @@ def _patch(module):
                     sq = seqs[si]
                     sid = int(getattr(sq, "seq_id", -1))
                     step = len(sq) - sq.num_prompt_tokens
-                    _PER_SEQ.setdefault(sid, []).append((step, picks[row], margins[row]))
+                    _PER_SEQ.setdefault(sid, []).append((step, picks[row], margins[row], tops[row]))
                     k = sid - int(os.environ.get("B200E2E_FIRST_SEQ_ID", "1"))   # earlier ids: warm-up sequences
                     if forced is not None and 0 <= k < len(forced) and step < len(forced[k]):
                         out[row] = forced[k][step]

@@ -97,8 +97,8 @@ def worker(a):
 def compare(ref_path, our_path, steps, tie_margin):
     """Greedy parity over `steps` decisions per sequence.  `our_path` is a TEACHER-FORCED run (it was fed
     the reference's tokens), so every decision of both arms was taken on an identical context: the
-    arg-max token ids must be identical, except where the top-2 logit margin is within `tie_margin`
-    (bf16 logits: one ulp at |x| in [2,4) is 0.0156) -- a tie that rounding legitimately flips.
+    arg-max token ids must be identical, except where the top-2 logit margin is within `tie_margin` in BOTH
+    arms -- a tie that rounding legitimately flips.
     Prints a JSON verdict; exit status 1 if any decision differs outside a near-tie."""
     ref, our = json.load(open(ref_path)), json.load(open(our_path))
     mref = json.load(open(ref_path + ".margins"))
@@ -108,8 +108,8 @@ def compare(ref_path, our_path, steps, tie_margin):
     seq_identical = 0
     worst, margins = [], []
     for i in range(n):
-        r = {st: (tok, mg) for st, tok, mg in mref[str(i + ref["first_seq_id"])]}
-        o = {st: (tok, mg) for st, tok, mg in mour[str(i + our["first_seq_id"])]}
+        r = {rec[0]: (rec[1], rec[2]) for rec in mref[str(i + ref["first_seq_id"])]}
+        o = {rec[0]: (rec[1], rec[2]) for rec in mour[str(i + our["first_seq_id"])]}
         ok_seq = True
         for st in range(steps):
             if st not in r or st not in o:
@@ -120,15 +120,27 @@ def compare(ref_path, our_path, steps, tie_margin):
                 same += 1
                 continue
             ok_seq = False
-            if min(r[st][1], o[st][1]) <= tie_margin:
+            if max(r[st][1], o[st][1]) <= tie_margin:             # a tie in BOTH arms
                 tie += 1
             else:
                 real += 1
             worst.append(dict(seq=i, step=st, ref_margin=round(r[st][1], 5), our_margin=round(o[st][1], 5)))
         seq_identical += ok_seq
+    # arm-to-arm logit noise on identical contexts: |top-1 logit of the reference - top-1 logit of the drop-in| over the
+    # decisions where both picked the same token (records carry the top-1 value as a fourth field)
+    noise = []
+    for i in range(n):
+        rr = {rec[0]: rec for rec in mref[str(i + ref["first_seq_id"])]}
+        oo = {rec[0]: rec for rec in mour[str(i + our["first_seq_id"])]}
+        for st in range(steps):
+            if st in rr and st in oo and len(rr[st]) > 3 and len(oo[st]) > 3 and rr[st][1] == oo[st][1]:
+                noise.append(abs(rr[st][3] - oo[st][3]))
+    noise.sort()
+    nq = lambda f: noise[min(int(len(noise) * f), len(noise) - 1)] if noise else None  # noqa: E731
     margins.sort()
     worst.sort(key=lambda d: -min(d["ref_margin"], d["our_margin"]))
     verdict = dict(sequences=n, steps=steps, decisions=total, identical=same, differ_at_near_tie=tie, differ_for_real=real,
+                   top1_logit_abs_diff=dict(p50=nq(0.5), p90=nq(0.9), p99=nq(0.99), max=nq(1.0)),
                    sequences_fully_identical=seq_identical, tie_margin=tie_margin, largest_margin_differences=worst[:8],
                    ref_margin_quantiles=dict(p0=margins[0], p1=margins[len(margins) // 100], p10=margins[len(margins) // 10],
                                              p50=margins[len(margins) // 2]) if margins else None,
@@ -152,8 +164,8 @@ def compare_free(ref_path, our_path, steps, tie_margin):
     compared = identical_seqs = ties = real = 0
     margins, first_div = [], []
     for i in range(n):
-        r = {st: (tok, mg) for st, tok, mg in mref[str(i + ref["first_seq_id"])]}
-        o = {st: (tok, mg) for st, tok, mg in mour[str(i + our["first_seq_id"])]}
+        r = {rec[0]: (rec[1], rec[2]) for rec in mref[str(i + ref["first_seq_id"])]}
+        o = {rec[0]: (rec[1], rec[2]) for rec in mour[str(i + our["first_seq_id"])]}
         tr, to = ref["token_ids"][i][:steps], our["token_ids"][i][:steps]
         div = next((t for t in range(min(len(tr), len(to))) if tr[t] != to[t]), None)
         upto = div if div is not None else min(len(tr), len(to))
