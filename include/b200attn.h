@@ -85,13 +85,23 @@ int b200_ar_status(void* comm, int32_t* status_out);
  * mapping (pass NULL).  After b200_nvls_create on every rank the host must run a group barrier before the first
  * call.  x [T, hidden] bf16: this rank's partial sums (any device memory); residual [T, hidden] bf16 updated in
  * place, or NULL (then v = float(s)); weight [hidden] bf16, or NULL together with residual for a plain all-reduce
- * (out <- s).  one_shot != 0: every rank reduces every row itself (one barrier; small messages); 0: reduce-scatter
- * + multicast all-gather inside the kernel (two barriers).  All ranks must pass the same shapes and form.
+ * (out <- s).  peer_bufs[world]: the unicast mappings of every rank's buffer (peer_bufs[rank] == local_buf), or NULL
+ * (then form 3 is unavailable).  b200_nvls_create zeroes the local buffer.
+ * form: 0 = reduce-scatter (multimem.ld_reduce) + multicast all-gather (multimem.st), two barriers;
+ *       1 = every rank multimem.ld_reduces every row itself, one barrier;
+ *       2 = "LL" one-shot: no barrier -- every rank multicasts {data, epoch} packets, readers spin on the epoch that
+ *           rides in the same 16-byte store as the data; sums in rank order (needs 2 x world x message <= one LL slot);
+ *       3 = "LL" two-shot: no barrier -- reduce-scatter by peer stores of packets, owner sums in rank order and
+ *           multicasts result packets (messages <= 4 MB).
+ *     Forms 2/3 move twice the bytes and save every barrier (~6 us each); their results are bit-identical on all
+ *     ranks and equal the fp32 sum in rank order rounded once; forms 0/1 round the switch's own fp32 sum once.
+ *     All ranks must pass the same shapes and form.
  * Stream-ordered, CUDA-graph capturable (slots alternate with a device-resident epoch), cooperative launch. */
 size_t b200_nvls_buffer_bytes(size_t max_msg_bytes);
-int b200_nvls_create(int rank, int world, void* local_buf, void* multicast_buf, size_t max_msg_bytes, void** comm_out);
+int b200_nvls_create(int rank, int world, void* local_buf, void* multicast_buf, void* const* peer_bufs,
+                     size_t max_msg_bytes, void** comm_out);
 int b200_nvls_allreduce_add_rmsnorm(void* comm, const void* x, void* residual, const void* weight, float eps, void* out,
-                                    int32_t num_tokens, int32_t hidden, int32_t one_shot, void* stream);
+                                    int32_t num_tokens, int32_t hidden, int32_t form, void* stream);
 int b200_nvls_status(void* comm, int32_t* status_out);
 int b200_nvls_destroy(void* comm);
 

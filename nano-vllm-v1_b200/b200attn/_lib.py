@@ -21,7 +21,7 @@ SIGNATURES = {
     "b200_ar_destroy": (c_int32, [c_void_p]),
     "b200_ar_status": (c_int32, [c_void_p, POINTER(c_int32)]),
     "b200_nvls_buffer_bytes": (c_size_t, [c_size_t]),
-    "b200_nvls_create": (c_int32, [c_int32, c_int32, c_void_p, c_void_p, c_size_t, POINTER(c_void_p)]),
+    "b200_nvls_create": (c_int32, [c_int32, c_int32, c_void_p, c_void_p, POINTER(c_void_p), c_size_t, POINTER(c_void_p)]),
     "b200_nvls_allreduce_add_rmsnorm": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_void_p,
                                                   c_int32, c_int32, c_int32, c_void_p]),
     "b200_nvls_status": (c_int32, [c_void_p, POINTER(c_int32)]),

@@ -462,7 +462,7 @@ class NvlsAllReduce:
         self.max_bytes = int(max_bytes)
         dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         nbytes = lib.b200_nvls_buffer_bytes(self.max_bytes)
-        mc_ptr = None
+        mc_ptr, peers = None, None
         if self.world > 1:
             import torch.distributed._symmetric_memory as symm_mem
             self.buf = symm_mem.empty(nbytes, dtype=torch.uint8, device=dev)
@@ -470,28 +470,60 @@ class NvlsAllReduce:
             mc_ptr = int(self.hdl.multicast_ptr)
             if not mc_ptr:
                 raise RuntimeError("b200attn: this group has no NVLS multicast mapping (multicast_ptr == 0)")
+            peers = (ctypes.c_void_p * self.world)(*[int(p) for p in self.hdl.buffer_ptrs])
+            assert int(self.hdl.buffer_ptrs[self.rank]) == self.buf.data_ptr()
         else:
             self.buf = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         comm = ctypes.c_void_p()
-        check(lib.b200_nvls_create(self.rank, self.world, self.buf.data_ptr(), mc_ptr, self.max_bytes,
+        check(lib.b200_nvls_create(self.rank, self.world, self.buf.data_ptr(), mc_ptr, peers, self.max_bytes,
                                    ctypes.byref(comm)), "b200_nvls_create")
         self._comm = comm
-        self.one_shot_budget = int(__import__("os").environ.get("B200ATTN_NVLS_ONE_SHOT_BUDGET", 3 << 19))
+        self.ll_max_bytes = min(self.max_bytes, 4 << 20)
+        env = __import__("os").environ
+        # thresholds measured with tools/nvls_check.py (profiles/r2_nvls_tp*.json): bytes a rank RECEIVES in the LL one-shot
+        # form; largest message of the LL two-shot form; extra bytes the one-shot barrier form may move to save a barrier
+        self.ll1_budget = int(env.get("B200ATTN_NVLS_LL1_BUDGET", 1 << 20))
+        self.ll2_max = min(int(env.get("B200ATTN_NVLS_LL2_MAX", 1 << 20)), self.ll_max_bytes)
+        self.one_shot_budget = int(env.get("B200ATTN_NVLS_ONE_SHOT_BUDGET", 3 << 19))
+        self.fused_max_pair = int(env.get("B200ATTN_NVLS_FUSED_MAX_TP2", 1 << 20))
+        self.forced_form = int(env["B200ATTN_NVLS_FORM"]) if "B200ATTN_NVLS_FORM" in env else None
         if self.world > 1:
-            dist.barrier(group)            # every rank zeroed its flags before anyone can signal (b200attn.h)
+            dist.barrier(group)            # every rank zeroed its buffer before anyone can write into it (b200attn.h)
 
-    def one_shot(self, nbytes: int) -> bool:
-        """Form policy, a pure function of (group size, message bytes): every rank reducing every row itself
-        moves (world - 2) x message more bytes over NVLink than reduce-scatter + multicast all-gather but saves
-        the second barrier (~5 us); at the measured 770 GB/s per direction that pays up to ~1.5 MB extra."""
-        return nbytes * max(self.world - 2, 0) <= self.one_shot_budget
+    def choose_form(self, nbytes: int) -> int:
+        """Form policy (include/b200attn.h), a pure function of (group size, message bytes) so every rank picks the
+        same: the flag-in-data forms save every barrier (~6 us each) and pay with twice the bytes on the wire --
+        one-shot (2) while the 2 x world x message bytes a rank receives stay small, two-shot (3) up to ~1 MB;
+        beyond that the in-switch reduction, every rank for itself (1) or reduce-scatter + all-gather (0)."""
+        if self.forced_form is not None:
+            return self.forced_form
+        if 2 * self.world * nbytes <= min(self.ll1_budget, 4 * self.ll_max_bytes):
+            return 2
+        if nbytes <= self.ll2_max:
+            return 3
+        return 1 if nbytes * max(self.world - 2, 0) <= self.one_shot_budget else 0
+
+    def form_fits(self, form: int, nbytes: int) -> bool:
+        """Whether `form` can carry a message of nbytes (the range checks of b200_nvls_allreduce_add_rmsnorm)."""
+        if form == 2:
+            return 2 * self.world * nbytes <= 4 * self.ll_max_bytes + 1024
+        if form == 3:
+            return nbytes <= self.ll_max_bytes
+        return form in (0, 1) and nbytes <= self.max_bytes
+
+    def pays(self, x: torch.Tensor) -> bool:
+        """Whether deferring RowParallelLinear's all-reduce of `x` into the RMSNorm launch beats the peer-memory
+        all-reduce followed by the RMSNorm kernel.  Measured (profiles/r2_nvls_tp2.json, r2_nvls_tp8.json): always at
+        TP8 (1.2-2.2x up to 4 MB); with two ranks only up to ~1 MB -- beyond, one posted peer store of the whole
+        message beats the round trips of multimem.ld_reduce."""
+        return self.fits(x) and (self.world > 2 or x.numel() * 2 <= self.fused_max_pair)
 
     def fits(self, x: torch.Tensor) -> bool:
         return (x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 2 and x.is_contiguous()
                 and x.shape[1] % 8 == 0 and x.shape[1] <= 16384 and 0 < x.numel() * 2 <= self.max_bytes)
 
     def all_reduce_add_rms_norm(self, x: torch.Tensor, residual: Optional[torch.Tensor], weight: Optional[torch.Tensor],
-                                eps: float, one_shot: Optional[bool] = None, out: Optional[torch.Tensor] = None):
+                                eps: float, form: Optional[int] = None, out: Optional[torch.Tensor] = None):
         """(normed, residual) like RMSNorm.forward(x_allreduced, residual); weight None => plain all-reduce -> out."""
         if not self.fits(x):
             raise RuntimeError("b200attn: tensor does not fit the NVLS fused all-reduce")
@@ -502,15 +534,15 @@ class NvlsAllReduce:
         if weight is not None:
             _need_cuda_bf16(weight, "weight")
             assert weight.is_contiguous() and weight.numel() == hidden
-        if one_shot is None:
-            one_shot = self.one_shot(x.numel() * 2)
+        if form is None:
+            form = self.choose_form(x.numel() * 2)
         if out is None:
             out = torch.empty_like(x)
         xin = x if x.data_ptr() % 16 == 0 else x.clone()
         check(self._lib.b200_nvls_allreduce_add_rmsnorm(
             self._comm, xin.data_ptr(), residual.data_ptr() if residual is not None else None,
             weight.data_ptr() if weight is not None else None, float(eps), out.data_ptr(), T, hidden,
-            1 if one_shot else 0, _stream()), "b200_nvls_allreduce_add_rmsnorm")
+            int(form), _stream()), "b200_nvls_allreduce_add_rmsnorm")
         return out if residual is None else (out, residual)
 
     def status(self) -> int:
@@ -590,7 +622,7 @@ def tp_row_parallel_output(y: torch.Tensor) -> torch.Tensor:
     flush_pending_all_reduce()                                  # an earlier deferred sum nobody normalised
     if _DEFER_DEPTH > 0:
         nv = tp_nvls()
-        if nv and nv.fits(y):
+        if nv and nv.pays(y):
             _PENDING = y
             return y
     return tp_all_reduce_(y)

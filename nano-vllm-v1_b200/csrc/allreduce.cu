@@ -81,6 +81,7 @@ __device__ __forceinline__ void ar_spin(const ArComm& c, F done) {
     uint64_t t0 = 0;
     for (uint32_t spins = 0; !done(); ++spins) {
         if ((spins & 1023u) == 1023u) {
+            if (*reinterpret_cast<volatile uint32_t*>(c.epoch + 7) != 0u) return;    // sticky: one timeout per communicator
             uint64_t now;
             asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
             if (t0 == 0) t0 = now;

@@ -632,11 +632,11 @@ def test_nvls_fused_allreduce_add_rmsnorm_world1(ops):
         want_y, want_r = ops.rms_norm(x, w, 1e-6, r.clone())
         oy, orr = oracle.add_rms_norm(x.cpu(), r.cpu(), w.cpu(), 1e-6)
         assert _ulp_ok(want_y, oy) and torch.equal(want_r.cpu(), orr)
-        for one_shot in (True, False, None):
+        for form in (1, 0, 2, 3, None, 2, 0, 3):              # every form, interleaved: the flag counters stay in step
             r2 = r.clone()
-            y, r3 = nv.all_reduce_add_rms_norm(x, r2, w, 1e-6, one_shot=one_shot)
-            assert r3 is r2 and torch.equal(r2, want_r) and _ulp_ok(y, oy), (T, H, one_shot)
-            assert (y == want_y).float().mean() > 0.99, (T, H, one_shot)
+            y, r3 = nv.all_reduce_add_rms_norm(x, r2, w, 1e-6, form=form)
+            assert r3 is r2 and torch.equal(r2, want_r) and _ulp_ok(y, oy), (T, H, form)
+            assert (y == want_y).float().mean() > 0.99, (T, H, form)
         assert torch.equal(nv.all_reduce_add_rms_norm(x, None, None, 0.0), x)          # plain all-reduce
         assert _ulp_ok(nv.all_reduce_add_rms_norm(x, None, w, 1e-6), oracle.rms_norm(x.cpu(), w.cpu(), 1e-6))
     x = torch.randn(16, 4096, generator=g, device="cuda").bfloat16()
@@ -651,7 +651,7 @@ def test_nvls_fused_allreduce_add_rmsnorm_world1(ops):
     gr = torch.cuda.CUDAGraph()
     with torch.cuda.graph(gr):
         nv.all_reduce_add_rms_norm(x, r, w, 1e-6, out=y)
-        nv.all_reduce_add_rms_norm(x, r, w, 1e-6, out=y, one_shot=False)
+        nv.all_reduce_add_rms_norm(x, r, w, 1e-6, out=y, form=3)
     r.copy_(r0)
     gr.replay()
     rr = r0.clone()
