@@ -31,6 +31,7 @@ struct PersistParams {
 };
 
 constexpr int PREFILL_EMU_DEFAULT = 0;
+constexpr int PREFILL_WGS_DEFAULT = 1;
 
 struct PsSmem {
     static constexpr int NQ = 2;
@@ -41,7 +42,10 @@ struct PsSmem {
     // q_full[2] q_empty[2] k_full[S] k_empty[S] v_full[S] v_empty[S] s_full[2] p_full[2] o_final[2] p_half[2]
     static constexpr int NUM_BARS = 6 * NQ + 4 * TC_KV_STAGES;
     static constexpr int TMEM_PTR_OFF = BAR_OFF + NUM_BARS * 8;
-    static constexpr int TOTAL = TMEM_PTR_OFF + 16;
+    // WGS == 2: row-maximum / row-sum exchange between the two half-row warpgroups of a query tile,
+    // float[2 buffers][2 tiles][2 halves][128 rows]
+    static constexpr int XCH_OFF = TMEM_PTR_OFF + 16;
+    static constexpr int TOTAL = XCH_OFF + 2 * 2 * 2 * 128 * 4;
     static constexpr int ALLOC = TOTAL + 1024;
 };
 
@@ -132,6 +136,20 @@ __device__ __forceinline__ uint32_t cvt_bf16x2(float lo, float hi) {
     return r;
 }
 
+// Named barriers over a subset of the CTA (ids 1..15; 0 is __syncthreads).
+__device__ __forceinline__ bool bar_red_or(uint32_t id, uint32_t nthreads, bool pred) {
+    uint32_t r;
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\tsetp.ne.b32 q, %3, 0;\n\t"
+        "bar.red.or.pred p, %1, %2, q;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(r) : "r"(id), "r"(nthreads), "r"((uint32_t)pred) : "memory");
+    return r != 0;
+}
+__device__ __forceinline__ void bar_sync_n(uint32_t id, uint32_t nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
 // 2^x for two values on the FMA/ALU pipes instead of MUFU.ex2 (which is co-critical with the tensor
 // pipe: 16 ex2/clk/SM).  x = n + r with n = floor(x) taken from the low mantissa bits of
 // (x + 1.5*2^23) rounded towards -inf, 2^r on [0,1) by a degree-3 polynomial (max relative error
@@ -156,9 +174,21 @@ __device__ __forceinline__ void exp2_poly2(float x0, float x1, float& p0, float&
     p1 = __uint_as_float(__float_as_uint(q1) + (__float_as_uint(t1) << 23));
 }
 
+constexpr int ps_threads(int wgs) { return wgs == 2 ? 576 : 384; }
+
 // EMU = how many of every 4 score pairs take the polynomial exp2 instead of MUFU.ex2 (0..4).
-template <int EMU, bool TRACE = false>
-__global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
+// WGS = softmax warpgroups per query tile.
+//   1: one thread owns a whole 128-column score row; 384 threads: warp 0 producer, 1 MMA, 2 TMEM allocator,
+//      4-11 softmax; setmaxnreg 80 / 208.
+//   2: two warpgroups split every row in halves of 64 columns; 576 threads: warps 0-15 softmax (tile = wg >> 1,
+//      half = wg & 1), 16 producer, 17 MMA + TMEM allocator; 112 registers each, no setmaxnreg.  The row maximum,
+//      the packing and the TMEM traffic of a tile take half as long, which shortens the
+//      S -> softmax -> P -> PV -> QK -> S chain that bounds this kernel.  Half h keeps its P over the first 32
+//      columns of ITS OWN 64 score columns (PV K-steps 4..7 read their A operand at +64), so the halves never
+//      touch each other's TMEM; they meet on a 64-thread named barrier that ORs the "row maximum outgrew the
+//      running one" predicate and exchange maxima through shared memory only when it fires.
+template <int EMU, bool TRACE = false, int WGS = 1>
+__global__ void __maxnreg__(WGS == 2 ? 112 : 168) prefill_persist_kernel(
     const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
     const __grid_constant__ CUtensorMap map_v, const PersistParams p) {
     using L = PsSmem;
@@ -183,7 +213,11 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
     volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(smem_gen + L::TMEM_PTR_OFF);
     constexpr uint32_t TMEM_COLS = 512;
 
-    if (warp == 1 && lane == 0) {
+    constexpr int PROD_WARP = WGS == 2 ? 16 : 0, MMA_WARP = WGS == 2 ? 17 : 1, ALLOC_WARP = WGS == 2 ? 17 : 2;
+    constexpr int INIT_WARP = WGS == 2 ? 16 : 1;
+    const bool is_softmax = WGS == 2 ? warp < 16 : warp >= 4;
+
+    if (warp == INIT_WARP && lane == 0) {
 #pragma unroll
         for (int t = 0; t < 2; ++t) {
             mbar_init(q_full(t), 1); mbar_init(q_empty(t), 1); mbar_init(s_full(t), 1);
@@ -194,10 +228,12 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
             mbar_init(k_full(s), 1); mbar_init(k_empty(s), 1); mbar_init(v_full(s), 1); mbar_init(v_empty(s), 1);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    } else if (warp == 2) {
+    }
+    if (warp == ALLOC_WARP) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_base + L::TMEM_PTR_OFF), "r"(TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-    } else if (warp == 0 && lane == 0) {
+    }
+    if (warp == PROD_WARP && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_q) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
@@ -207,9 +243,9 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
 
-    if (warp < 4) {
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
-        if (warp == 0) {
+    if (!is_softmax) {
+        if constexpr (WGS == 1) asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
+        if (warp == PROD_WARP) {
             // ===================================== TMA producer =====================================
             if (lane == 0) {
                 const bool paged = p.block_tables != nullptr;
@@ -247,7 +283,7 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
                     }
                 }
             }
-        } else if (warp == 1) {
+        } else if (warp == MMA_WARP) {
             // ===================================== MMA issuer =======================================
             if (lane == 0) {
                 constexpr uint32_t IDESC_QK = umma_idesc(0);           // B = K tile, K-major
@@ -266,7 +302,7 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
                     const uint32_t d = tmem_base + t * 256 + 128, a = tmem_base + t * 256;
 #pragma unroll
                     for (int kk = 4 * half; kk < 4 * half + 4; ++kk)
-                        tc_mma_ts(d, a + kk * 8, umma_desc(vst + kk * 2048, TC_HALF_BYTES, 1024), IDESC_PV, (!first || kk > 0));
+                        tc_mma_ts(d, a + (WGS == 2 && kk >= 4 ? 64 + (kk - 4) * 8 : kk * 8), umma_desc(vst + kk * 2048, TC_HALF_BYTES, 1024), IDESC_PV, (!first || kk > 0));
                 };
                 uint32_t kv_it = 0, q_use[2] = {0, 0}, p_cnt[2] = {0, 0};
                 auto stamp = [&](int t, uint32_t n, int e) {
@@ -326,6 +362,181 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
                     }
                     kv_it += u.n_max;
                 }
+            }
+        }
+    } else if constexpr (WGS == 2) {
+        // ============ softmax + correction + epilogue, two half-row warpgroups per query tile ============
+        const int wg = warp >> 2;                                   // 0..3
+        const int t = wg >> 1, h = wg & 1;                          // query tile, column half
+        const int wq = warp & 3;                                    // TMEM lane quarter this warp may touch
+        const int row_in_tile = wq * 32 + lane;
+        // my 64 score columns; my P (bf16x2) overlays the first 32 of them; my 64 output columns are at +128
+        const uint32_t tB = tmem_base + t * 256 + 64 * h + ((uint32_t)(wq * 32) << 16);
+        const uint32_t pair_bar = 1 + t * 4 + wq;                   // the two warps that share these 32 rows
+        const uint32_t my_p_bar = h == 0 ? p_half(t) : p_full(t);   // K-steps 0..3 of PV read half 0, 4..7 half 1
+        float* xch = reinterpret_cast<float*>(smem_gen + L::XCH_OFF) + t * 256 + row_in_tile;
+        uint32_t xpar = 0;                                          // exchange buffer parity (same in both halves)
+        const uint64_t scale2 = pack2(p.scale_log2, p.scale_log2);
+        uint32_t s_cnt = 0, o_cnt = 0, kv_it = 0;
+        auto stamp = [&](uint32_t n, int e) {
+            if (TRACE && blockIdx.x == 0 && h == 0 && row_in_tile == 0 && (int)n < p.trace_tiles) p.trace[(t * p.trace_tiles + n) * 8 + e] = clock64();
+        };
+        Unit u;
+        for (int k = 0; get_round(p, k, u); ++k) {
+            const int nt = u.nt(t);
+            const int r_begin = u.rbegin(t);
+            const int row = r_begin + row_in_tile;                  // query index within the sequence
+            const int offset = u.Lk - u.Lq;
+            float m_used = -INFINITY;                               // running maximum, scaled (log2) domain
+            uint64_t l2 = pack2(0.f, 0.f);                          // two partial sums of MY half of the row
+
+            for (int j = 0; j < nt; ++j) {
+                const int n0 = j * TC_BN;
+                stamp(s_cnt, 0);
+                mbar_wait(s_full(t), s_cnt & 1u);
+                stamp(s_cnt, 1);
+                ++s_cnt;
+                tc_fence_after();
+                uint32_t s[64];
+                tmem_ld32(tB, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
+                tmem_ld32(tB + 32, *reinterpret_cast<uint32_t(*)[32]>(&s[32]));
+                tmem_wait_ld();
+                stamp(s_cnt - 1, 2);
+                if ((n0 + TC_BN > u.Lk) || (n0 + TC_BN - 1 > r_begin + offset)) {      // tail or diagonal tile
+                    const int lim = min(u.Lk - 1, row + offset) - n0 - 64 * h;         // last visible column of my half
+#pragma unroll
+                    for (int i = 0; i < 64; ++i)
+                        if (i > lim) s[i] = 0xff800000u;                                // -inf
+                }
+                float mxc[4];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) mxc[c] = -INFINITY;
+#pragma unroll
+                for (int i = 0; i < 64; i += 8)
+#pragma unroll
+                    for (int c = 0; c < 4; ++c)
+                        mxc[c] = max3(mxc[c], __uint_as_float(s[i + 2 * c]), __uint_as_float(s[i + 2 * c + 1]));
+                const float mx = max3(mxc[0], mxc[1], fmaxf(mxc[2], mxc[3])) * p.scale_log2;
+                // lazy rescale: keep exponentiating against m_used until some row's max outgrows it by 2^8.
+                // The barrier tells both halves whether ANY of the 32 rows needs the slow path.
+                const bool grow = mx > m_used + TC_RESCALE_THRESHOLD || (m_used == -INFINITY && mx > -INFINITY);
+                if (bar_red_or(pair_bar, 64, grow)) {
+                    float* slot = xch + xpar * 512;
+                    xpar ^= 1u;
+                    slot[h * 128] = mx;
+                    bar_sync_n(pair_bar, 64);
+                    const float m_new = fmaxf(m_used, fmaxf(mx, slot[(h ^ 1) * 128]));
+                    const float alpha = fast_exp2(m_used - (m_new == -INFINITY ? 0.f : m_new));   // 0 when m_used = -inf
+                    l2 = mul2(l2, pack2(alpha, alpha));
+                    m_used = m_new;
+                    if (j > 0) {                                    // PV(j-1) completed before s_full(j) fired
+                        const uint64_t a2 = pack2(alpha, alpha);
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {               // 16 columns at a time: this rare path must not
+                            uint32_t o[16];                         // raise the register peak of the common one
+                            tmem_ld16(tB + 128 + c * 16, o);
+                            tmem_wait_ld();
+#pragma unroll
+                            for (int i = 0; i < 16; i += 2) {
+                                float a, b;
+                                unpack2(mul2(pack2(__uint_as_float(o[i]), __uint_as_float(o[i + 1])), a2), a, b);
+                                o[i] = __float_as_uint(a); o[i + 1] = __float_as_uint(b);
+                            }
+                            tmem_st16(tB + 128 + c * 16, o);
+                        }
+                        // PV(j) K-steps 0..3 start on half 0's arrival alone and accumulate into ALL of O:
+                        // neither half may arrive before both have finished rescaling.
+                        tmem_wait_st();
+                        tc_fence_before();
+                        bar_sync_n(pair_bar, 64);
+                        tc_fence_after();
+                    }
+                }
+                stamp(s_cnt - 1, 3);
+                const float neg_m = m_used == -INFINITY ? 0.f : -m_used;
+                const uint64_t negm2 = pack2(neg_m, neg_m);
+                if (n0 + TC_BN > u.Lk) {
+                    // Rows of the V tile past the context may hold NaN garbage (torch.empty cache):
+                    // 0 * NaN would poison O, so zero them in shared memory before PV reads them.
+                    const uint32_t it = kv_it + j, st = it % S;
+                    mbar_wait(v_full(st), (it / S) & 1u);
+                    uint8_t* vt = smem_gen + L::V_OFF + st * TC_TILE_BYTES;
+                    const int first = u.Lk - n0;                    // first invalid row of this tile
+                    for (int idx = row_in_tile; idx < (TC_BN - first) * 16; idx += 128) {
+                        const int r = first + (idx >> 4), c16 = idx & 15;
+                        *reinterpret_cast<int4*>(vt + (c16 >> 3) * TC_HALF_BYTES + r * 128 + (c16 & 7) * 16) = make_int4(0, 0, 0, 0);
+                    }
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                }
+                {
+                    constexpr int EXP_LAG = 6;
+                    uint64_t acc1 = pack2(0.f, 0.f);
+                    uint32_t pk[8];
+#pragma unroll
+                    for (int i = 0; i < 32 + EXP_LAG; ++i) {
+                        if (i < 32) {
+                            float x0, x1, p0, p1;
+                            unpack2(fma2(pack2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), scale2, negm2), x0, x1);
+                            if ((i & 3) < EMU) exp2_poly2(x0, x1, p0, p1);
+                            else { p0 = fast_exp2(x0); p1 = fast_exp2(x1); }
+                            s[2 * i] = __float_as_uint(p0); s[2 * i + 1] = __float_as_uint(p1);
+                        }
+                        if (i >= EXP_LAG) {
+                            const int kk = i - EXP_LAG;
+                            const float p0 = __uint_as_float(s[2 * kk]), p1 = __uint_as_float(s[2 * kk + 1]);
+                            if (kk & 1) acc1 = add2(acc1, pack2(p0, p1));
+                            else l2 = add2(l2, pack2(p0, p1));
+                            pk[kk & 7] = cvt_bf16x2(p0, p1);
+                            if ((kk & 7) == 7) tmem_st8(tB + (kk >> 3) * 8, pk);
+                        }
+                    }
+                    l2 = add2(l2, acc1);
+                }
+                stamp(s_cnt - 1, 4);
+                tmem_wait_st();
+                tc_fence_before();
+                mbar_arrive(my_p_bar);
+                stamp(s_cnt - 1, 5);
+            }
+            kv_it += u.n_max;
+
+            // ---- epilogue: O / l -> bf16 -> global (rows beyond the sequence are dropped) --------
+            if (nt > 0) {
+                float la, lb;
+                unpack2(l2, la, lb);
+                const float l_mine = la + lb;
+                float* slot = xch + xpar * 512;
+                xpar ^= 1u;
+                slot[h * 128] = l_mine;
+                bar_sync_n(pair_bar, 64);
+                const float l_other = slot[(h ^ 1) * 128];
+                const float l_sum = h == 0 ? l_mine + l_other : l_other + l_mine;    // half 0 + half 1 in both
+                mbar_wait(o_final(t), o_cnt & 1u);
+                ++o_cnt;
+                tc_fence_after();
+                const float inv = l_sum > 1e-30f ? 1.f / l_sum : 0.f;  // see exp2_poly2 on masked scores
+                __nv_bfloat16* orow = p.out + (int64_t)(u.q0 + row) * p.out_token_stride + (int64_t)u.head(t) * B200_HD + 64 * h;
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t o[32];
+                    tmem_ld32(tB + 128 + c * 32, o);
+                    tmem_wait_ld();
+                    if (row < u.Lq) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            int4 v;
+                            v.x = (int)cvt_bf16x2(__uint_as_float(o[8 * i + 0]) * inv, __uint_as_float(o[8 * i + 1]) * inv);
+                            v.y = (int)cvt_bf16x2(__uint_as_float(o[8 * i + 2]) * inv, __uint_as_float(o[8 * i + 3]) * inv);
+                            v.z = (int)cvt_bf16x2(__uint_as_float(o[8 * i + 4]) * inv, __uint_as_float(o[8 * i + 5]) * inv);
+                            v.w = (int)cvt_bf16x2(__uint_as_float(o[8 * i + 6]) * inv, __uint_as_float(o[8 * i + 7]) * inv);
+                            *reinterpret_cast<int4*>(orow + c * 32 + i * 8) = v;
+                        }
+                    }
+                }
+                // O(t) is overwritten by the next unit's first PV, which waits on half 0's next arrival; half 0
+                // cannot get there before BOTH halves pass the pair barrier of the next unit's first tile,
+                // i.e. after both epilogues have read their columns.
+                tc_fence_before();
             }
         }
     } else {
@@ -499,7 +710,7 @@ __global__ void __launch_bounds__(384, 1) prefill_persist_kernel(
     // ---- teardown --------------------------------------------------------------------------------
     tc_fence_before();
     __syncthreads();
-    if (warp == 2) {
+    if (warp == ALLOC_WARP) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
     }
@@ -523,21 +734,27 @@ int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32
     if (a.batch == 0 || a.total_q == 0 || a.max_q == 0) return 0;
     if (get_encode_fn() == nullptr) return -6;
     using KernelFn = void (*)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const PersistParams);
-    static const KernelFn kernels[5] = {prefill_persist_kernel<0>, prefill_persist_kernel<1>, prefill_persist_kernel<2>,
-                                        prefill_persist_kernel<3>, prefill_persist_kernel<4>};
-    static int emu = -1;
+    static const KernelFn kernels[2][5] = {
+        {prefill_persist_kernel<0, false, 1>, prefill_persist_kernel<1, false, 1>, prefill_persist_kernel<2, false, 1>,
+         prefill_persist_kernel<3, false, 1>, prefill_persist_kernel<4, false, 1>},
+        {prefill_persist_kernel<0, false, 2>, prefill_persist_kernel<1, false, 2>, prefill_persist_kernel<2, false, 2>,
+         prefill_persist_kernel<3, false, 2>, prefill_persist_kernel<4, false, 2>}};
+    static int emu = -1, wgs = -1;
     static PerDeviceOnce once;                                   // the shared-memory opt-in is per device
     if (once.need()) {
-        for (int i = 0; i < 5; ++i) {
-            cudaError_t e = cudaFuncSetAttribute(kernels[i], cudaFuncAttributeMaxDynamicSharedMemorySize, PsSmem::ALLOC);
-            if (e != cudaSuccess) return (int)e;
-        }
+        for (int w = 0; w < 2; ++w)
+            for (int i = 0; i < 5; ++i) {
+                cudaError_t e = cudaFuncSetAttribute(kernels[w][i], cudaFuncAttributeMaxDynamicSharedMemorySize, PsSmem::ALLOC);
+                if (e != cudaSuccess) return (int)e;
+            }
         once.done();
     }
     if (emu < 0) {
         const char* env = getenv("B200ATTN_PREFILL_EMU");        // A/B knob; default chosen by measurement
         int v = env ? atoi(env) : PREFILL_EMU_DEFAULT;
         emu = v < 0 ? 0 : (v > 4 ? 4 : v);
+        env = getenv("B200ATTN_PREFILL_WGS");                    // softmax warpgroups per query tile (1 or 2)
+        wgs = (env ? atoi(env) : PREFILL_WGS_DEFAULT) == 2 ? 2 : 1;
     }
     const bool paged = a.block_tables != nullptr;
     const CUtensorMap* pq = cached_map(a.q, (uint64_t)a.total_q, (uint64_t)a.Hq, (uint64_t)a.q_token_stride);
@@ -566,12 +783,14 @@ int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32
     if (g_trace != nullptr) {
         static PerDeviceOnce trace_once;
         if (trace_once.need()) {
-            cudaFuncSetAttribute(prefill_persist_kernel<PREFILL_EMU_DEFAULT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, PsSmem::ALLOC);
+            cudaFuncSetAttribute(prefill_persist_kernel<PREFILL_EMU_DEFAULT, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, PsSmem::ALLOC);
+            cudaFuncSetAttribute(prefill_persist_kernel<PREFILL_EMU_DEFAULT, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, PsSmem::ALLOC);
             trace_once.done();
         }
-        prefill_persist_kernel<PREFILL_EMU_DEFAULT, true><<<grid, 384, PsSmem::ALLOC, stream>>>(mq, mk, mv, p);
+        if (wgs == 2) prefill_persist_kernel<PREFILL_EMU_DEFAULT, true, 2><<<grid, ps_threads(2), PsSmem::ALLOC, stream>>>(mq, mk, mv, p);
+        else prefill_persist_kernel<PREFILL_EMU_DEFAULT, true, 1><<<grid, ps_threads(1), PsSmem::ALLOC, stream>>>(mq, mk, mv, p);
     } else {
-        kernels[emu]<<<grid, 384, PsSmem::ALLOC, stream>>>(mq, mk, mv, p);
+        kernels[wgs - 1][emu]<<<grid, ps_threads(wgs), PsSmem::ALLOC, stream>>>(mq, mk, mv, p);
     }
     return (int)cudaGetLastError();
 }
