@@ -174,7 +174,13 @@ __device__ __forceinline__ void exp2_poly2(float x0, float x1, float& p0, float&
     p1 = __uint_as_float(__float_as_uint(q1) + (__float_as_uint(t1) << 23));
 }
 
-constexpr int ps_threads(int wgs) { return wgs == 2 ? 576 : 384; }
+constexpr int ps_threads(int wgs) { return wgs == 2 ? 640 : 384; }
+#ifndef PS_W2_LOW
+#define PS_W2_LOW 64
+#define PS_W2_HIGH 104
+#endif
+#define PS_STR2(x) #x
+#define PS_STR(x) PS_STR2(x)
 
 // EMU = how many of every 4 score pairs take the polynomial exp2 instead of MUFU.ex2 (0..4).
 // WGS = softmax warpgroups per query tile.
@@ -188,7 +194,7 @@ constexpr int ps_threads(int wgs) { return wgs == 2 ? 576 : 384; }
 //      touch each other's TMEM; they meet on a 64-thread named barrier that ORs the "row maximum outgrew the
 //      running one" predicate and exchange maxima through shared memory only when it fires.
 template <int EMU, bool TRACE = false, int WGS = 1>
-__global__ void __maxnreg__(WGS == 2 ? 112 : 168) prefill_persist_kernel(
+__global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
     const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
     const __grid_constant__ CUtensorMap map_v, const PersistParams p) {
     using L = PsSmem;
@@ -245,6 +251,7 @@ __global__ void __maxnreg__(WGS == 2 ? 112 : 168) prefill_persist_kernel(
 
     if (!is_softmax) {
         if constexpr (WGS == 1) asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
+        else asm volatile("setmaxnreg.dec.sync.aligned.u32 " PS_STR(PS_W2_LOW) ";");
         if (warp == PROD_WARP) {
             // ===================================== TMA producer =====================================
             if (lane == 0) {
@@ -365,6 +372,7 @@ __global__ void __maxnreg__(WGS == 2 ? 112 : 168) prefill_persist_kernel(
             }
         }
     } else if constexpr (WGS == 2) {
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 " PS_STR(PS_W2_HIGH) ";");
         // ============ softmax + correction + epilogue, two half-row warpgroups per query tile ============
         const int wg = warp >> 2;                                   // 0..3
         const int t = wg >> 1, h = wg & 1;                          // query tile, column half
