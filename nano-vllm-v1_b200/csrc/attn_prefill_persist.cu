@@ -179,6 +179,10 @@ constexpr int ps_threads(int wgs) { return wgs == 2 ? 640 : 384; }
 #define PS_W2_LOW 64
 #define PS_W2_HIGH 104
 #endif
+#ifndef PS_W1_LOW
+#define PS_W1_LOW 80
+#define PS_W1_HIGH 208
+#endif
 #define PS_STR2(x) #x
 #define PS_STR(x) PS_STR2(x)
 
@@ -250,7 +254,7 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
     const uint32_t tmem_base = *tmem_ptr_smem;
 
     if (!is_softmax) {
-        if constexpr (WGS == 1) asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
+        if constexpr (WGS == 1) asm volatile("setmaxnreg.dec.sync.aligned.u32 " PS_STR(PS_W1_LOW) ";");
         else asm volatile("setmaxnreg.dec.sync.aligned.u32 " PS_STR(PS_W2_LOW) ";");
         if (warp == PROD_WARP) {
             // ===================================== TMA producer =====================================
@@ -295,21 +299,22 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
             if (lane == 0) {
                 constexpr uint32_t IDESC_QK = umma_idesc(0);           // B = K tile, K-major
                 constexpr uint32_t IDESC_PV = umma_idesc(1);           // B = V tile, MN-major
+                constexpr uint32_t DESC_HI = umma_desc_hi(1024);
                 auto issue_qk = [&](int t, uint32_t st) {
-                    const uint32_t kst = sK + st * TC_TILE_BYTES, qst = sQ + t * TC_TILE_BYTES;
+                    const uint32_t k_lo = umma_desc_lo(sK + st * TC_TILE_BYTES, 0), q_lo = umma_desc_lo(sQ + t * TC_TILE_BYTES, 0);
                     const uint32_t d = tmem_base + t * 256;
 #pragma unroll
                     for (int ks = 0; ks < 8; ++ks) {
-                        const uint32_t off = (ks >> 2) * TC_HALF_BYTES + (ks & 3) * 32;
-                        tc_mma_ss(d, umma_desc(qst + off, 0, 1024), umma_desc(kst + off, 0, 1024), IDESC_QK, ks > 0);
+                        const uint32_t off = ((ks >> 2) * TC_HALF_BYTES + (ks & 3) * 32) >> 4;
+                        tc_mma_ss2(d, q_lo + off, k_lo + off, DESC_HI, IDESC_QK, ks > 0);
                     }
                 };
                 auto issue_pv = [&](int t, uint32_t st, bool first, int half) {     // K-steps 4*half .. 4*half+3
-                    const uint32_t vst = sV + st * TC_TILE_BYTES;
+                    const uint32_t v_lo = umma_desc_lo(sV + st * TC_TILE_BYTES, TC_HALF_BYTES);
                     const uint32_t d = tmem_base + t * 256 + 128, a = tmem_base + t * 256;
 #pragma unroll
                     for (int kk = 4 * half; kk < 4 * half + 4; ++kk)
-                        tc_mma_ts(d, a + (WGS == 2 && kk >= 4 ? 64 + (kk - 4) * 8 : kk * 8), umma_desc(vst + kk * 2048, TC_HALF_BYTES, 1024), IDESC_PV, (!first || kk > 0));
+                        tc_mma_ts2(d, a + (WGS == 2 && kk >= 4 ? 64 + (kk - 4) * 8 : kk * 8), v_lo + kk * (2048 >> 4), DESC_HI, IDESC_PV, (!first || kk > 0));
                 };
                 uint32_t kv_it = 0, q_use[2] = {0, 0}, p_cnt[2] = {0, 0};
                 auto stamp = [&](int t, uint32_t n, int e) {
@@ -548,7 +553,7 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
             }
         }
     } else {
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 " PS_STR(PS_W1_HIGH) ";");
         // ======================== softmax + correction + epilogue warpgroups =====================
         const int t = (warp - 4) >> 2;                              // query tile of this warpgroup
         const int wq = warp & 3;                                    // TMEM lane quarter this warp may touch

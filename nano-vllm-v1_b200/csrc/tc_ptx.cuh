@@ -76,6 +76,27 @@ __device__ __forceinline__ void tc_mma_ts(uint32_t d, uint32_t a, uint64_t b, ui
         "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
         ::"r"(d), "r"(a), "l"(b), "r"(idesc), "r"(acc) : "memory");
 }
+// Same two instructions with the shared-memory descriptors passed as (low word, high word): the 64-bit value is
+// assembled inside the volatile block, so the compiler cannot precompute one descriptor per (tile, K-step, stage)
+// outside the issue loop and then spill them (the MMA warp lives on a small setmaxnreg budget) -- a descriptor
+// costs one integer add on its low word instead of a local-memory reload in front of every tcgen05.mma.
+__device__ __forceinline__ void tc_mma_ss2(uint32_t d, uint32_t a_lo, uint32_t b_lo, uint32_t hi, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}"
+        ::"r"(d), "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void tc_mma_ts2(uint32_t d, uint32_t a, uint32_t b_lo, uint32_t hi, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], db, %4, p;\n\t}"
+        ::"r"(d), "r"(a), "r"(b_lo), "r"(hi), "r"(idesc), "r"(acc) : "memory");
+}
+// low / high words of umma_desc(addr, lbo, sbo)
+__device__ __forceinline__ uint32_t umma_desc_lo(uint32_t smem_addr, uint32_t lbo) { return ((smem_addr & 0x3FFFFu) >> 4) | ((lbo >> 4) << 16); }
+__host__ __device__ constexpr uint32_t umma_desc_hi(uint32_t sbo) { return (sbo >> 4) | (1u << 14) | (2u << 29); }
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x32.b32 "

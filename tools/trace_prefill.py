@@ -15,8 +15,12 @@ from b200attn import ops, load_library
 ap = argparse.ArgumentParser()
 ap.add_argument("--tiles", type=int, default=96)
 ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "prefill_trace.json"))
+ap.add_argument("--solo", action="store_true", help="one query tile per CTA (odd group, 128-row chunks over a long prefix): "
+                "softmax warpgroup 0 runs with no second softmax warp on its SM sub-partitions")
 a = ap.parse_args()
 B, L, Hq, Hkv, D, P = 4, 4096, 32, 8, 128, 256
+if a.solo:
+    B, L, Hq, Hkv = 40, 8192, 4, 4
 g = torch.Generator(device="cuda").manual_seed(0)
 nb = B * L // P
 kc = torch.randn(nb, P, Hkv, D, generator=g, device="cuda", dtype=torch.bfloat16)
@@ -24,8 +28,15 @@ vc = torch.randn(nb, P, Hkv, D, generator=g, device="cuda", dtype=torch.bfloat16
 q = torch.randn(B * L, Hq, D, generator=g, device="cuda", dtype=torch.bfloat16)
 bt = torch.arange(nb, dtype=torch.int32, device="cuda").view(B, -1)
 cu = torch.arange(0, (B + 1) * L, L, dtype=torch.int32, device="cuda")
-plan = ops.attn_plan(cu, cu, B * L, Hq, Hkv, route_decode=True)
-run = lambda: ops.attn_varlen_planned(q, kc, vc, cu, cu, L, L, D ** -0.5, block_table=bt, plan=plan)  # noqa: E731
+if a.solo:
+    LQ = 128
+    q = q[:B * LQ].contiguous()
+    cuq = torch.arange(0, (B + 1) * LQ, LQ, dtype=torch.int32, device="cuda")
+    plan = ops.attn_plan(cuq, cu, B * LQ, Hq, Hkv, route_decode=True)
+    run = lambda: ops.attn_varlen_planned(q, kc, vc, cuq, cu, LQ, L, D ** -0.5, block_table=bt, plan=plan)  # noqa: E731
+else:
+    plan = ops.attn_plan(cu, cu, B * L, Hq, Hkv, route_decode=True)
+    run = lambda: ops.attn_varlen_planned(q, kc, vc, cu, cu, L, L, D ** -0.5, block_table=bt, plan=plan)  # noqa: E731
 for _ in range(3):
     run()
 torch.cuda.synchronize()
@@ -40,16 +51,18 @@ t0 = int(t[t > 0].min())
 rel = torch.where(t > 0, t - t0, torch.zeros_like(t))
 names = ["wait S", "S ready->loaded", "max (+mask/rescale)", "exp+cvt+st issue", "st wait+fence+arrive"]
 lo, hi = a.tiles // 4, a.tiles - 2
-for wg in (0, 1):
+for wg in ((0,) if a.solo else (0, 1)):
     r = rel[wg, lo:hi].double()
     d = (r[:, 1:6] - r[:, 0:5])
     per = (r[1:, 1] - r[:-1, 1])
     print(f"softmax WG{wg}: tile period median {per.median().item():.0f} cyc;",
           ", ".join(f"{n} {d[:, i].median().item():.0f}" for i, n in enumerate(names)))
-for wg in (0, 1):
+for wg in ((0,) if a.solo else (0, 1)):
     r = rel[2 + wg, lo:hi].double()
     print(f"MMA issuer for WG{wg}: waits for P {((r[:, 1] - r[:, 0]).median().item()):.0f} cyc, issue PV+QK {((r[:, 2] - r[:, 1]).median().item()):.0f} cyc,"
           f" P published -> seen {(rel[2 + wg, lo:hi, 1] - rel[wg, lo:hi, 5]).double().median().item():.0f}")
+if a.solo:
+    sys.exit(0)
 r = rel[2, lo:hi].double()
 print(f"MMA issuer loop top: wait V(j) {(r[:, 5] - r[:, 4]).median().item():.0f} cyc, wait K(j+1) {(r[:, 6] - r[:, 5]).median().item():.0f} cyc,"
       f" previous tile's last issue -> loop top {(rel[2, lo + 1:hi + 1, 4] - rel[3, lo:hi, 2]).double().median().item():.0f} cyc")
