@@ -180,8 +180,8 @@ constexpr int ps_threads(int wgs) { return wgs == 2 ? 640 : 384; }
 #define PS_W2_HIGH 104
 #endif
 #ifndef PS_W1_LOW
-#define PS_W1_LOW 80
-#define PS_W1_HIGH 208
+#define PS_W1_LOW 72
+#define PS_W1_HIGH 216
 #endif
 #define PS_STR2(x) #x
 #define PS_STR(x) PS_STR2(x)
@@ -587,6 +587,11 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
                 for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&s[c * 32]));
                 tmem_wait_ld();
                 stamp(s_cnt - 1, 2);
+                if constexpr (TRACE) {                              // stamp 6: all four score loads have really landed
+                    uint32_t dep = s[0] ^ s[31] ^ s[32] ^ s[63] ^ s[64] ^ s[95] ^ s[96] ^ s[127];
+                    asm volatile("" ::"r"(dep) : "memory");
+                    stamp(s_cnt - 1, 6);
+                }
                 if ((n0 + TC_BN > u.Lk) || (n0 + TC_BN - 1 > r_begin + offset)) {      // tail or diagonal tile
                     const int lim = min(u.Lk - 1, row + offset) - n0;                  // last visible column of this row
 #pragma unroll
@@ -604,6 +609,10 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
                         mxc[c] = max3(mxc[c], __uint_as_float(s[i + 2 * c]), __uint_as_float(s[i + 2 * c + 1]));
                 const float mx0 = max3(mxc[0], mxc[1], mxc[2]), mx1 = max3(mxc[3], mxc[4], mxc[5]);
                 const float mx = max3(mx0, mx1, fmaxf(mxc[6], mxc[7])) * p.scale_log2;
+                if constexpr (TRACE) {                              // stamp 7: row maximum known
+                    asm volatile("" ::"f"(mx) : "memory");
+                    stamp(s_cnt - 1, 7);
+                }
                 // lazy rescale: keep exponentiating against m_used until some row's max outgrows it by 2^8
                 const bool grow = mx > m_used + TC_RESCALE_THRESHOLD || (m_used == -INFINITY && mx > -INFINITY);
                 if (__any_sync(0xffffffffu, grow)) {

@@ -57,6 +57,9 @@ for wg in ((0,) if a.solo else (0, 1)):
     per = (r[1:, 1] - r[:-1, 1])
     print(f"softmax WG{wg}: tile period median {per.median().item():.0f} cyc;",
           ", ".join(f"{n} {d[:, i].median().item():.0f}" for i, n in enumerate(names)))
+    if (r[:, 6] > 0).all():
+        print(f"   inside the max phase: loads issued -> all landed {(r[:, 6] - r[:, 2]).median().item():.0f}, landed -> row max known "
+              f"{(r[:, 7] - r[:, 6]).median().item():.0f}, max known -> phase end {(r[:, 3] - r[:, 7]).median().item():.0f}")
 for wg in ((0,) if a.solo else (0, 1)):
     r = rel[2 + wg, lo:hi].double()
     print(f"MMA issuer for WG{wg}: waits for P {((r[:, 1] - r[:, 0]).median().item()):.0f} cyc, issue PV+QK {((r[:, 2] - r[:, 1]).median().item()):.0f} cyc,"

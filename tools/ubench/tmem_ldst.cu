@@ -46,6 +46,26 @@ __global__ void k(long long* cycles, uint32_t* sink, int iters) {
 #pragma unroll
             for (int c = 0; c < NLD; ++c) acc += r[c][0] ^ r[c][31];        // dependent uses of the first and last register of each load
         }
+        if (MODE == 3) {                                          // the prefill softmax's load + row-maximum phase
+#pragma unroll
+            for (int c = 0; c < 4; ++c) LD32(base + c * 32, r[c]);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            float mc[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) mc[c] = __uint_as_float(acc);
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+#pragma unroll
+                for (int i = 0; i < 32; i += 16)
+#pragma unroll
+                    for (int q = 0; q < 8; ++q)
+                        asm("max.f32 %0, %0, %1, %2;" : "+f"(mc[q]) : "f"(__uint_as_float(r[c][i + 2 * q])), "f"(__uint_as_float(r[c][i + 2 * q + 1])));
+            float m;
+            asm("max.f32 %0, %1, %2, %3;" : "=f"(m) : "f"(mc[0]), "f"(mc[1]), "f"(mc[2]));
+            asm("max.f32 %0, %0, %1, %2;" : "+f"(m) : "f"(mc[3]), "f"(mc[4]));
+            asm("max.f32 %0, %0, %1, %2;" : "+f"(m) : "f"(mc[5]), "f"(mc[6]));
+            acc = __float_as_uint(fmaxf(m, mc[7])) & 0x7fffffu;
+        }
         if (MODE == 1 || MODE == 2) {
 #pragma unroll
             for (int c = 0; c < NLD; ++c) { r[c][0] += acc; ST32(base + c * 32, r[c]); }
@@ -83,6 +103,7 @@ int main() {
         run<1, 2>("st.x32 + wait", threads);
         run<1, 4>("st.x32 + wait", threads);
         run<2, 4>("ld + st round trip", threads);
+        run<3, 4>("ld x4 + wait + 67 max3", threads);
     }
     return 0;
 }
