@@ -30,7 +30,7 @@ __global__ void __launch_bounds__(PLAN_THREADS) attn_plan_kernel(
     if (threadIdx.x == 0) n_decode = 0;
     __syncthreads();
     int32_t* decode_rows = plan + PLAN_HEADER_WORDS;
-    int32_t* items = decode_rows + batch;
+    int32_t* items = plan + plan_items_offset(batch);
 
     auto key_of = [tile_rows](int mt, int Lq, int Lk) {
         const int kv_end = min(Lk, (mt + 1) * tile_rows + (Lk - Lq));
@@ -88,7 +88,11 @@ __global__ void __launch_bounds__(PLAN_THREADS) attn_plan_kernel(
         const int tiles = (Lq + tile_rows - 1) / tile_rows;
         for (int mt = tiles - 1; mt >= 0; --mt) {
             const int pos = atomicAdd(&hist[key_of(mt, Lq, Lk)], 1);
-            if (pos < max_items) { items[2 * pos] = b; items[2 * pos + 1] = mt; }
+            if (pos < max_items) {
+                int4* rec = reinterpret_cast<int4*>(items + PLAN_ITEM_WORDS * pos);
+                rec[0] = make_int4(b, mt, cu_q[b], Lq);
+                rec[1] = make_int4(cu_k[b], Lk, 0, 0);
+            }
         }
     }
 }

@@ -45,7 +45,11 @@ struct PsSmem {
     // WGS == 2: row-maximum / row-sum exchange between the two half-row warpgroups of a query tile,
     // float[2 buffers][2 tiles][2 halves][128 rows]
     static constexpr int XCH_OFF = TMEM_PTR_OFF + 16;
-    static constexpr int TOTAL = XCH_OFF + 2 * 2 * 2 * 128 * 4;
+    // WGS == 1: output staging, one [128 rows][64 bf16] half tile (16 KB, 16-byte chunks XOR-swizzled by row) per
+    // softmax warpgroup, so the epilogue's global stores are whole 128-byte lines.  Same bytes as XCH (never both).
+    static constexpr int STAGE_OFF = (XCH_OFF + 127) & ~127;
+    static constexpr int STAGE_BYTES = 128 * 128;
+    static constexpr int TOTAL = STAGE_OFF + 2 * STAGE_BYTES;
     static constexpr int ALLOC = TOTAL + 1024;
 };
 
@@ -63,19 +67,30 @@ struct Unit {
 // direction of every other round pairs a CTA's heavy units with light ones (static LPT-like balance).
 __device__ __forceinline__ int snake(int k, int c, int g) { return (k & 1) ? (k + 1) * g - 1 - c : k * g + c; }
 
-// Work unit w of this launch.  Every role evaluates this itself (a handful of cached loads).
-__device__ __forceinline__ bool get_unit(const PersistParams& p, int w, Unit& u) {
-    const int n_items = __ldg(p.plan);
-    const int per_item = p.pair_heads ? (p.Hq >> 1) : p.Hq;
-    if (w >= n_items * per_item) return false;
-    const int item = w / per_item;
-    const int sub = w - item * per_item;
-    u.b = __ldg(p.items + 2 * item);
-    const int mt = __ldg(p.items + 2 * item + 1);
-    u.q0 = __ldg(p.cu_q + u.b);
-    u.Lq = __ldg(p.cu_q + u.b + 1) - u.q0;
-    u.k0 = __ldg(p.cu_k + u.b);
-    u.Lk = __ldg(p.cu_k + u.b + 1) - u.k0;
+// Work unit w of this launch.  Every role walks the same list on its own.  A unit's record is fetched in one
+// load level (two 16-byte loads of the plan's item record) one unit AHEAD: on this part an L2 hit costs
+// ~800 cycles, and three dependent levels (count -> item -> cu_seqlens) in front of every unit left the tensor
+// pipe idle for ~3,000 cycles per unit while the MMA issuer found out what to do next.
+struct RawUnit { int4 a; int4 b; };          // {sequence, tile, q0, Lq} {k0, Lk, -, -}
+__device__ __forceinline__ int units_per_item(const PersistParams& p) { return p.pair_heads ? (p.Hq >> 1) : p.Hq; }
+__device__ __forceinline__ RawUnit fetch_unit(const PersistParams& p, int w, int n_units) {
+    RawUnit r;
+    r.a = make_int4(0, 0, 0, 0); r.b = r.a;
+    if (w < n_units) {
+        // volatile asm: an ordinary read-only load is free to be sunk to its first use (the next unit's start),
+        // which is exactly the latency this fetch-ahead exists to hide
+        const int4* rec = reinterpret_cast<const int4*>(p.items) + 2 * (w / units_per_item(p));
+        asm volatile("ld.global.nc.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(r.a.x), "=r"(r.a.y), "=r"(r.a.z), "=r"(r.a.w) : "l"(rec));
+        asm volatile("ld.global.nc.v2.s32 {%0,%1}, [%2];" : "=r"(r.b.x), "=r"(r.b.y) : "l"(rec + 1));
+    }
+    return r;
+}
+__device__ __forceinline__ void decode_unit(const PersistParams& p, int w, const RawUnit& r, Unit& u) {
+    const int per_item = units_per_item(p);
+    const int sub = w - (w / per_item) * per_item;
+    u.b = r.a.x;
+    const int mt = r.a.y;
+    u.q0 = r.a.z; u.Lq = r.a.w; u.k0 = r.b.x; u.Lk = r.b.y;
     if (p.pair_heads) {
         u.head0 = 2 * sub; u.head1 = 2 * sub + 1;
         u.r0 = u.r1 = mt * TC_BM;
@@ -92,14 +107,27 @@ __device__ __forceinline__ bool get_unit(const PersistParams& p, int w, Unit& u)
     u.n_t0 = (kv_end0 + TC_BN - 1) / TC_BN;
     u.n_t1 = (kv_end1 + TC_BN - 1) / TC_BN;
     u.n_max = max(u.n_t0, u.n_t1);
-    return true;
 }
 
 // A CTA stops at its first out-of-range round: if snake(k, c) >= n then n < (k+1)*g, so every index of
 // every later round is out of range as well.
-__device__ __forceinline__ bool get_round(const PersistParams& p, int k, Unit& u) {
-    return get_unit(p, snake(k, (int)blockIdx.x, (int)gridDim.x), u);
-}
+struct UnitWalk {
+    int n_units, k; RawUnit raw;
+    __device__ __forceinline__ void begin(const PersistParams& p) {
+        n_units = __ldg(p.plan) * units_per_item(p);
+        k = 0;
+        raw = fetch_unit(p, snake(0, (int)blockIdx.x, (int)gridDim.x), n_units);
+    }
+    // Decodes the unit of this round into u (false: no more work) and starts the fetch of the next round's record.
+    __device__ __forceinline__ bool next(const PersistParams& p, Unit& u) {
+        const int w = snake(k, (int)blockIdx.x, (int)gridDim.x);
+        if (w >= n_units) return false;
+        decode_unit(p, w, raw, u);
+        ++k;
+        raw = fetch_unit(p, snake(k, (int)blockIdx.x, (int)gridDim.x), n_units);
+        return true;
+    }
+};
 
 // ---- packed f32x2 arithmetic (sm_100: FFMA2 / FADD2) and 3-input max ---------------------------
 __device__ __forceinline__ uint64_t pack2(float lo, float hi) {
@@ -261,11 +289,19 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
             if (lane == 0) {
                 const bool paged = p.block_tables != nullptr;
                 uint32_t kv_it = 0, q_use0 = 0, q_use1 = 0;
+                int tiles0 = 0;                                  // TRACE: tile index (of query tile 0) this unit starts at
+                auto pstamp = [&](int e) {
+                    if (TRACE && blockIdx.x == 0 && tiles0 < p.trace_tiles) p.trace[(3 * p.trace_tiles + tiles0) * 8 + e] = clock64();
+                };
                 Unit u;
-                for (int k = 0; get_round(p, k, u); ++k) {
+                UnitWalk walk;
+                walk.begin(p);
+                while (walk.next(p, u)) {
                     const int kvh = u.kvh;
+                    pstamp(6);                                   // producer holds this unit's descriptor
                     if (u.n_t0 > 0) {
                         mbar_wait(q_empty(0), (q_use0 & 1u) ^ 1u);
+                        pstamp(4);                               // Q slot 0 free -> Q load issued
                         ++q_use0;
                         mbar_expect_tx(q_full(0), TC_TILE_BYTES);
                         tma_load_3d(sQ, &map_q, q_full(0), 0, u.head0, u.q0 + u.r0);
@@ -284,6 +320,7 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
                         const int row = paged ? __ldg(bt + n0 / B200_PAGE) * B200_PAGE + (n0 & (B200_PAGE - 1)) : u.k0 + n0;
                         const uint32_t st = kv_it % S, par = (kv_it / S) & 1u;
                         mbar_wait(k_empty(st), par ^ 1u);
+                        if (j == 0) pstamp(5);                   // first K tile of the unit issued
                         mbar_expect_tx(k_full(st), TC_TILE_BYTES);
                         tma_load_3d(sK + st * TC_TILE_BYTES, &map_k, k_full(st), 0, kvh, row);
                         tma_load_3d(sK + st * TC_TILE_BYTES + TC_HALF_BYTES, &map_k, k_full(st), 64, kvh, row);
@@ -292,6 +329,7 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
                         tma_load_3d(sV + st * TC_TILE_BYTES, &map_v, v_full(st), 0, kvh, row);
                         tma_load_3d(sV + st * TC_TILE_BYTES + TC_HALF_BYTES, &map_v, v_full(st), 64, kvh, row);
                     }
+                    tiles0 += u.n_t0;
                 }
             }
         } else if (warp == MMA_WARP) {
@@ -321,13 +359,17 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
                     if (TRACE && blockIdx.x == 0 && (int)n < p.trace_tiles) p.trace[((2 + t) * p.trace_tiles + n) * 8 + e] = clock64();
                 };
                 Unit u;
-                for (int k = 0; get_round(p, k, u); ++k) {
+                UnitWalk walk;
+                walk.begin(p);
+                while (walk.next(p, u)) {
+                    stamp(0, p_cnt[0], 7);                       // issuer holds this unit's descriptor
 #pragma unroll
                     for (int t = 0; t < 2; ++t)
                         if (u.nt(t) > 0) { mbar_wait(q_full(t), q_use[t] & 1u); ++q_use[t]; }
                     if (u.n_max > 0) {
                         const uint32_t st0 = kv_it % S;
                         mbar_wait(k_full(st0), (kv_it / S) & 1u);
+                        stamp(1, p_cnt[0], 7);                   // Q and K(0) landed: first QK goes out
                         tc_fence_after();
 #pragma unroll
                         for (int t = 0; t < 2; ++t)
@@ -395,7 +437,9 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
             if (TRACE && blockIdx.x == 0 && h == 0 && row_in_tile == 0 && (int)n < p.trace_tiles) p.trace[(t * p.trace_tiles + n) * 8 + e] = clock64();
         };
         Unit u;
-        for (int k = 0; get_round(p, k, u); ++k) {
+        UnitWalk walk;
+        walk.begin(p);
+        while (walk.next(p, u)) {
             const int nt = u.nt(t);
             const int r_begin = u.rbegin(t);
             const int row = r_begin + row_in_tile;                  // query index within the sequence
@@ -567,7 +611,9 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
             if (TRACE && blockIdx.x == 0 && row_in_tile == 0 && (int)n < p.trace_tiles) p.trace[(t * p.trace_tiles + n) * 8 + e] = clock64();
         };
         Unit u;
-        for (int k = 0; get_round(p, k, u); ++k) {
+        UnitWalk walk;
+        walk.begin(p);
+        while (walk.next(p, u)) {
             const int nt = u.nt(t);
             const int r_begin = u.rbegin(t);
             const int row = r_begin + row_in_tile;                  // query index within the sequence
@@ -695,33 +741,64 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
             }
             kv_it += u.n_max;
 
-            // ---- epilogue: O / l -> bf16 -> global (rows beyond the sequence are dropped) --------
+            // ---- epilogue: O / l -> bf16 -> shared staging -> global, whole 128-byte lines ----------------
+            // (a thread owns a ROW of O; storing it straight to global memory is 16 bytes per row per
+            // instruction, 32 partial sectors per warp store -- measured ~6,000 cycles per tile, during which
+            // this warpgroup cannot start the next unit.)  Two passes of 64 columns through a 16 KB buffer.
+            auto estamp = [&](int e) {                              // TRACE rows 4/5: epilogue of the unit's last tile
+                if (TRACE && blockIdx.x == 0 && row_in_tile == 0 && s_cnt > 0 && (int)(s_cnt - 1) < p.trace_tiles)
+                    p.trace[((4 + t) * p.trace_tiles + (s_cnt - 1)) * 8 + e] = clock64();
+            };
             if (nt > 0) {
+                estamp(0);
                 mbar_wait(o_final(t), o_cnt & 1u);
+                estamp(1);
                 ++o_cnt;
                 tc_fence_after();
                 float la, lb;
                 unpack2(l2, la, lb);
                 const float l_sum = la + lb;
                 const float inv = l_sum > 1e-30f ? 1.f / l_sum : 0.f;  // see exp2_poly2 on masked scores
-                __nv_bfloat16* orow = p.out + (int64_t)(u.q0 + row) * p.out_token_stride + (int64_t)u.head(t) * B200_HD;
+                const uint64_t inv2 = pack2(inv, inv);
+                uint8_t* stage = smem_gen + L::STAGE_OFF + t * L::STAGE_BYTES;
+                const int tid_wg = (warp & 3) * 32 + lane;          // == row_in_tile
+                const int rows_valid = min(TC_BM, u.Lq - r_begin);  // rows of this tile inside the sequence
+                __nv_bfloat16* obase = p.out + (int64_t)(u.q0 + r_begin) * p.out_token_stride + (int64_t)u.head(t) * B200_HD;
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    uint32_t o[32];
-                    tmem_ld32(tO + c * 32, o);
-                    tmem_wait_ld();
-                    if (row < u.Lq) {
+                for (int pass = 0; pass < 2; ++pass) {
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
+                        uint32_t o[32];
+                        tmem_ld32(tO + pass * 64 + c * 32, o);
+                        tmem_wait_ld();
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
+                            float f[8];
+#pragma unroll
+                            for (int q = 0; q < 8; q += 2)
+                                unpack2(mul2(pack2(__uint_as_float(o[8 * i + q]), __uint_as_float(o[8 * i + q + 1])), inv2), f[q], f[q + 1]);
                             int4 v;
-                            v.x = (int)cvt_bf16x2(__uint_as_float(o[8 * i + 0]) * inv, __uint_as_float(o[8 * i + 1]) * inv);
-                            v.y = (int)cvt_bf16x2(__uint_as_float(o[8 * i + 2]) * inv, __uint_as_float(o[8 * i + 3]) * inv);
-                            v.z = (int)cvt_bf16x2(__uint_as_float(o[8 * i + 4]) * inv, __uint_as_float(o[8 * i + 5]) * inv);
-                            v.w = (int)cvt_bf16x2(__uint_as_float(o[8 * i + 6]) * inv, __uint_as_float(o[8 * i + 7]) * inv);
-                            *reinterpret_cast<int4*>(orow + c * 32 + i * 8) = v;
+                            v.x = (int)cvt_bf16x2(f[0], f[1]); v.y = (int)cvt_bf16x2(f[2], f[3]);
+                            v.z = (int)cvt_bf16x2(f[4], f[5]); v.w = (int)cvt_bf16x2(f[6], f[7]);
+                            const int chunk = c * 4 + i;            // 16-byte chunk of this row's 128 staged bytes
+                            *reinterpret_cast<int4*>(stage + row_in_tile * 128 + ((chunk ^ (row_in_tile & 7)) << 4)) = v;
                         }
                     }
+                    estamp(2 + 2 * pass);
+                    bar_sync_n(1 + t, 128);                          // the half tile is staged
+#pragma unroll
+                    for (int step = 0; step < 8; ++step) {
+                        const int r = step * 16 + (tid_wg >> 3), chunk = tid_wg & 7;
+                        if (r < rows_valid) {
+                            const int4 v = *reinterpret_cast<const int4*>(stage + r * 128 + ((chunk ^ (r & 7)) << 4));
+                            *reinterpret_cast<int4*>(obase + (int64_t)r * p.out_token_stride + pass * 64 + chunk * 8) = v;
+                        }
+                    }
+                    estamp(3 + 2 * pass);
+                    if (pass == 0) bar_sync_n(1 + t, 128);           // staging is free again
                 }
+                // The next unit's epilogue writes the staging buffer only after ITS o_final, i.e. after every
+                // thread of this warpgroup has arrived on p_full at least once more => the reads above are done.
                 // O(t) is overwritten by the next unit's first PV, which waits on this warpgroup's
                 // next p_full arrival (program order) => the reads above are complete by then.
                 tc_fence_before();
@@ -796,7 +873,7 @@ int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32
     p.out = (__nv_bfloat16*)a.out; p.out_token_stride = a.out_token_stride;
     p.Hq = a.Hq; p.G = a.Hq / a.Hkv; p.scale_log2 = a.scale * 1.4426950408889634f;
     p.pair_heads = plan_tile_rows(a.Hq, a.Hkv) == 128 ? 1 : 0;
-    p.plan = plan; p.items = plan + PLAN_HEADER_WORDS + a.batch;
+    p.plan = plan; p.items = plan + plan_items_offset(a.batch);
     int64_t units = (int64_t)max_items * (p.pair_heads ? a.Hq / 2 : a.Hq);
     int grid = sm_count();
     if (units < grid) grid = (int)units;
@@ -820,7 +897,7 @@ int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32
 }  // namespace b200
 
 // Debug only: when `dev_buf` (int64[4][max_tiles][8], zeroed by the caller) is non-null, the next
-// persistent prefill launches run the TRACE build and CTA 0 stamps clock64 at the phase boundaries of
+// (int64[6][max_tiles][8] since the epilogue rows were added) persistent prefill launches run the TRACE build and CTA 0 stamps clock64 at the phase boundaries of
 // its first `max_tiles` tiles (rows 0/1: softmax warpgroups, rows 2/3: the MMA issuer's view of them).
 extern "C" int b200_debug_prefill_trace(void* dev_buf, int max_tiles) {
     b200::g_trace = (long long*)dev_buf;

@@ -71,15 +71,20 @@ bool prefill_tc_available();
 
 // ---- step plan (attn_plan.cu) + persistent tcgen05 prefill (attn_prefill_persist.cu) ----------
 // plan buffer, int32 words: [0] n_items  [1] n_decode_rows  [2] tile_rows  [3..15] reserved
-//                           [16 .. 16 + batch)        rows with exactly one query token
-//                           [.. + 2*max_items)        (sequence, query tile) pairs, heaviest first; plan[2] = tile rows
+//                           [16 .. 16 + batch)        rows with exactly one query token (region padded to 4 words)
+//                           [.. + 8*max_items)        one 32-byte record per (sequence, query tile) work item, heaviest
+//                                                     first: {sequence, tile, q0, Lq, k0, Lk, 0, 0} -- everything the
+//                                                     prefill kernel needs about an item in ONE load level, so it can
+//                                                     fetch the next unit's record while the current unit runs
 constexpr int PLAN_HEADER_WORDS = 16;
+constexpr int PLAN_ITEM_WORDS = 8;
+constexpr size_t plan_items_offset(int32_t batch) { return (size_t)PLAN_HEADER_WORDS + (((size_t)batch + 3) & ~(size_t)3); }
 constexpr int PLAN_TILE_ROWS_MIN = 128;
 // tile rows of a launch: 128 when two q heads of one kv head share a CTA (even GQA group), else 256
 inline int32_t plan_tile_rows(int32_t Hq, int32_t Hkv) { return ((Hq / Hkv) % 2 == 0) ? 128 : 256; }
 inline int32_t plan_max_items(int32_t batch, int32_t total_q) { return total_q / PLAN_TILE_ROWS_MIN + batch; }
 inline size_t plan_bytes(int32_t batch, int32_t total_q) {
-    return ((size_t)PLAN_HEADER_WORDS + 2 * (size_t)plan_max_items(batch, total_q) + (size_t)batch) * sizeof(int32_t);
+    return (plan_items_offset(batch) + PLAN_ITEM_WORDS * (size_t)plan_max_items(batch, total_q)) * sizeof(int32_t);
 }
 int launch_attn_plan(const int32_t* cu_q, const int32_t* cu_k, int32_t batch, int32_t route_decode, int32_t tile_rows,
                      int32_t* plan, int32_t max_items, cudaStream_t stream);

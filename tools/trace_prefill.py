@@ -41,7 +41,7 @@ for _ in range(3):
     run()
 torch.cuda.synchronize()
 lib = load_library()
-buf = torch.zeros(4, a.tiles, 8, dtype=torch.int64, device="cuda")
+buf = torch.zeros(6, a.tiles, 8, dtype=torch.int64, device="cuda")
 lib.b200_debug_prefill_trace(buf.data_ptr(), a.tiles)
 run()
 torch.cuda.synchronize()
