@@ -526,8 +526,7 @@ def burst_and_sustained(run, device, world, burst_iters=15, sustained_ms=400.0):
     flush = torch.zeros(256 * 1024 * 1024 // 4, dtype=torch.int32, device=device)
     ts = []
     for _ in range(burst_iters):
-        flush.max()
-        torch.cuda.synchronize()
+        flush.max()                                    # (also hides the host side of the launch: the events see the kernel)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         run()
