@@ -30,7 +30,7 @@ PEAK = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exi
     {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}
 
 
-def timeit(fn, iters=20, warm=5, flush=None):
+def timeit(fn, iters=20, warm=int(os.environ.get("BK_WARM", "5")), flush=None):
     for _ in range(warm):
         fn()
     torch.cuda.synchronize()
