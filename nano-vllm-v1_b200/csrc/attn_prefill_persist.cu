@@ -211,6 +211,9 @@ constexpr int ps_threads(int wgs) { return wgs == 2 ? 640 : 384; }
 #define PS_W1_LOW 72
 #define PS_W1_HIGH 216
 #endif
+#ifndef PS_CROSS_UNIT
+#define PS_CROSS_UNIT 1
+#endif
 #define PS_STR2(x) #x
 #define PS_STR(x) PS_STR2(x)
 
@@ -358,34 +361,45 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
                 auto stamp = [&](int t, uint32_t n, int e) {
                     if (TRACE && blockIdx.x == 0 && (int)n < p.trace_tiles) p.trace[((2 + t) * p.trace_tiles + n) * 8 + e] = clock64();
                 };
-                Unit u;
+                // Cross-unit pipelining: in a unit's final K/V iteration, right after a query tile's last PV, the
+                // FIRST QK of the next unit for that tile is issued (its Q tile and K tile 0 were staged by the
+                // producer about one tile earlier), so the softmax warpgroup finds S ready when it returns from its
+                // epilogue instead of waiting for the other tile to finish and for this thread to walk to the next
+                // unit.  Only the final iteration may do this: earlier, the producer can still be held up by a
+                // barrier that this thread commits later in the same iteration (deadlock).
+                Unit u, un;
                 UnitWalk walk;
                 walk.begin(p);
-                while (walk.next(p, u)) {
+                bool have = walk.next(p, u);
+                bool pre[2] = {false, false};                   // first QK of unit `u`, tile t, already issued
+                while (have) {
+                    const bool have_n = walk.next(p, un);       // record fetched one unit ago
                     stamp(0, p_cnt[0], 7);                       // issuer holds this unit's descriptor
-#pragma unroll
-                    for (int t = 0; t < 2; ++t)
-                        if (u.nt(t) > 0) { mbar_wait(q_full(t), q_use[t] & 1u); ++q_use[t]; }
                     if (u.n_max > 0) {
                         const uint32_t st0 = kv_it % S;
-                        mbar_wait(k_full(st0), (kv_it / S) & 1u);
-                        stamp(1, p_cnt[0], 7);                   // Q and K(0) landed: first QK goes out
-                        tc_fence_after();
+                        bool waited_k = false;
 #pragma unroll
                         for (int t = 0; t < 2; ++t)
-                            if (u.nt(t) > 0) {
+                            if (u.nt(t) > 0 && !pre[t]) {
+                                mbar_wait(q_full(t), q_use[t] & 1u); ++q_use[t];
+                                if (!waited_k) { mbar_wait(k_full(st0), (kv_it / S) & 1u); waited_k = true; }
+                                tc_fence_after();
                                 issue_qk(t, st0);
                                 tc_commit(s_full(t));
                                 if (u.nt(t) == 1) tc_commit(q_empty(t));
                             }
-                        tc_commit(k_empty(st0));
+                        stamp(1, p_cnt[0], 7);
+                        tc_commit(k_empty(st0));                 // covers the QKs issued ahead during the previous unit too
                     }
+                    pre[0] = pre[1] = false;
+                    const uint32_t st0n = (kv_it + u.n_max) % S, par0n = ((kv_it + u.n_max) / S) & 1u;
                     for (int j = 0; j < u.n_max; ++j) {
                         const uint32_t it = kv_it + j, st = it % S, par = (it / S) & 1u;
+                        const bool final_it = j + 1 == u.n_max;
                         stamp(0, p_cnt[0], 4);
                         mbar_wait(v_full(st), par);
                         stamp(0, p_cnt[0], 5);
-                        if (j + 1 < u.n_max) mbar_wait(k_full((it + 1) % S), ((it + 1) / S) & 1u);
+                        if (!final_it) mbar_wait(k_full((it + 1) % S), ((it + 1) / S) & 1u);
                         stamp(0, p_cnt[0], 6);
                         tc_fence_after();
 #pragma unroll
@@ -410,11 +424,21 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
                                 }
                                 stamp(t, p_cnt[t] - 1, 2);
                             }
+                            if (PS_CROSS_UNIT && final_it && have_n && un.nt(t) > 0) {
+                                mbar_wait(q_full(t), q_use[t] & 1u); ++q_use[t];
+                                mbar_wait(k_full(st0n), par0n);
+                                tc_fence_after();
+                                issue_qk(t, st0n);
+                                tc_commit(s_full(t));
+                                if (un.nt(t) == 1) tc_commit(q_empty(t));
+                                pre[t] = true;
+                            }
                         }
                         tc_commit(v_empty(st));
-                        if (j + 1 < u.n_max) tc_commit(k_empty((it + 1) % S));
+                        if (!final_it) tc_commit(k_empty((it + 1) % S));
                     }
                     kv_it += u.n_max;
+                    u = un; have = have_n;
                 }
             }
         }
