@@ -26,6 +26,7 @@ struct PersistParams {
     const int32_t* cu_q; const int32_t* cu_k; const int32_t* block_tables; int32_t bt_row_stride;
     __nv_bfloat16* out; int64_t out_token_stride;
     int32_t Hq, G, pair_heads; float scale_log2;
+    uint32_t per_item, per_item_magic, g_magic16;   // units per item; ceil(2^32 / per_item); ceil(2^16 / G): exact division by multiply-high
     const int32_t* plan; const int32_t* items;
     long long* trace; int32_t trace_tiles;      // TRACE builds only: clock64 stamps of CTA 0 (b200_debug_prefill_trace)
 };
@@ -72,22 +73,26 @@ __device__ __forceinline__ int snake(int k, int c, int g) { return (k & 1) ? (k 
 // ~800 cycles, and three dependent levels (count -> item -> cu_seqlens) in front of every unit left the tensor
 // pipe idle for ~3,000 cycles per unit while the MMA issuer found out what to do next.
 struct RawUnit { int4 a; int4 b; };          // {sequence, tile, q0, Lq} {k0, Lk, -, -}
-__device__ __forceinline__ int units_per_item(const PersistParams& p) { return p.pair_heads ? (p.Hq >> 1) : p.Hq; }
+__device__ __forceinline__ int units_per_item(const PersistParams& p) { return (int)p.per_item; }
+// floor(w / per_item) without a division sequence (~100 cycles of dependent MUFU/convert work each, four of them per
+// unit boundary in every role): exact while w * per_item < 2^32, i.e. for any launch the plan can describe.
+__device__ __forceinline__ int item_of(const PersistParams& p, int w) {
+    return p.per_item == 1 ? w : (int)__umulhi((uint32_t)w, p.per_item_magic);
+}
 __device__ __forceinline__ RawUnit fetch_unit(const PersistParams& p, int w, int n_units) {
     RawUnit r;
     r.a = make_int4(0, 0, 0, 0); r.b = r.a;
     if (w < n_units) {
         // volatile asm: an ordinary read-only load is free to be sunk to its first use (the next unit's start),
         // which is exactly the latency this fetch-ahead exists to hide
-        const int4* rec = reinterpret_cast<const int4*>(p.items) + 2 * (w / units_per_item(p));
+        const int4* rec = reinterpret_cast<const int4*>(p.items) + 2 * item_of(p, w);
         asm volatile("ld.global.nc.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(r.a.x), "=r"(r.a.y), "=r"(r.a.z), "=r"(r.a.w) : "l"(rec));
         asm volatile("ld.global.nc.v2.s32 {%0,%1}, [%2];" : "=r"(r.b.x), "=r"(r.b.y) : "l"(rec + 1));
     }
     return r;
 }
 __device__ __forceinline__ void decode_unit(const PersistParams& p, int w, const RawUnit& r, Unit& u) {
-    const int per_item = units_per_item(p);
-    const int sub = w - (w / per_item) * per_item;
+    const int sub = w - item_of(p, w) * units_per_item(p);
     u.b = r.a.x;
     const int mt = r.a.y;
     u.q0 = r.a.z; u.Lq = r.a.w; u.k0 = r.b.x; u.Lk = r.b.y;
@@ -98,7 +103,7 @@ __device__ __forceinline__ void decode_unit(const PersistParams& p, int w, const
         u.head0 = u.head1 = sub;
         u.r0 = mt * 2 * TC_BM; u.r1 = u.r0 + TC_BM;
     }
-    u.kvh = u.head0 / p.G;
+    u.kvh = (int)(((uint32_t)u.head0 * p.g_magic16) >> 16);       // head0 / G, exact for head0, G <= 128
     const int offset = u.Lk - u.Lq;
     int kv_end0 = min(u.Lk, u.r0 + TC_BM + offset);
     if (u.r0 >= u.Lq || kv_end0 < 0) kv_end0 = 0;
@@ -212,7 +217,7 @@ constexpr int ps_threads(int wgs) { return wgs == 2 ? 640 : 384; }
 #define PS_W1_HIGH 216
 #endif
 #ifndef PS_CROSS_UNIT
-#define PS_CROSS_UNIT 1
+#define PS_CROSS_UNIT 0
 #endif
 #define PS_STR2(x) #x
 #define PS_STR(x) PS_STR2(x)
@@ -638,6 +643,8 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
         UnitWalk walk;
         walk.begin(p);
         while (walk.next(p, u)) {
+            if (TRACE && blockIdx.x == 0 && row_in_tile == 0 && s_cnt > 0 && (int)(s_cnt - 1) < p.trace_tiles)   // unit decoded
+                p.trace[((4 + t) * p.trace_tiles + (s_cnt - 1)) * 8 + 7] = clock64();
             const int nt = u.nt(t);
             const int r_begin = u.rbegin(t);
             const int row = r_begin + row_in_tile;                  // query index within the sequence
@@ -826,6 +833,7 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
                 // O(t) is overwritten by the next unit's first PV, which waits on this warpgroup's
                 // next p_full arrival (program order) => the reads above are complete by then.
                 tc_fence_before();
+                estamp(6);
             }
         }
     }
@@ -897,6 +905,9 @@ int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32
     p.out = (__nv_bfloat16*)a.out; p.out_token_stride = a.out_token_stride;
     p.Hq = a.Hq; p.G = a.Hq / a.Hkv; p.scale_log2 = a.scale * 1.4426950408889634f;
     p.pair_heads = plan_tile_rows(a.Hq, a.Hkv) == 128 ? 1 : 0;
+    p.per_item = (uint32_t)(p.pair_heads ? a.Hq / 2 : a.Hq);
+    p.per_item_magic = p.per_item <= 1 ? 0u : (uint32_t)((0x100000000ull + p.per_item - 1) / p.per_item);
+    p.g_magic16 = (uint32_t)((65536 + p.G - 1) / p.G);
     p.plan = plan; p.items = plan + plan_items_offset(a.batch);
     int64_t units = (int64_t)max_items * (p.pair_heads ? a.Hq / 2 : a.Hq);
     int grid = sm_count();
