@@ -58,10 +58,10 @@ __global__ void __launch_bounds__(256) kv_scatter_kernel(
 //      Lane l owns elements [8l, 8l+8) of the low half and [64+8l, 64+8l+8) of the high half,
 //      i.e. both members of eight NeoX rotation pairs => two 16-byte loads + two 16-byte stores
 //      per lane, no cross-lane traffic for the rotation, a 3-step butterfly for the sum of squares.
-//      Grid-stride over rows with a one-row software pipeline: the loads of the next row (data, position,
-//      slot) are in flight while the current one is normalised, rotated and stored.  Narrowing conversions
-//      are packed F2FP (ALU pipe), never F2F (quarter-rate XU pipe): the kernel is as much issue-bound as
-//      HBM-bound (16 elements per lane go through two roundings and an un-fused rotation).
+//      A warp walks the heads of one (token, head segment) unit four at a time with the loads of the next two
+//      head-quads in flight (2 KB per warp; 4 CTAs per SM => 64 KB per SM, what ~800 ns of HBM latency needs);
+//      the grid is exactly one wave of resident CTAs (a 4/3-wave grid cost 8 %).  Narrowing conversions are
+//      packed F2FP (ALU pipe), never F2F (quarter-rate XU pipe).
 //      Roundings follow layernorm.py:85-93 and rotary_embedding.py:60-65 exactly:
 //      bf16(x*rstd), bf16(.*w), fp32 rotate (un-fused mul/sub), bf16.
 // ------------------------------------------------------------------------------------------
@@ -78,129 +78,129 @@ struct KvStoreArgs {
 __device__ __forceinline__ float bf_lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf_hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
 
-struct RowLoad {                                   // everything one (token, head) row needs from memory, issued up front
-    int4 lo, hi;                                   // elements [8s, 8s+8) and [64+8s, 64+8s+8) of the row
-    const float* cs;                               // cos/sin row of the token's position (+ 8 * sub)
-    __nv_bfloat16* dst; __nv_bfloat16* cache_dst;
-    bool live, is_q, is_v;
-};
+// Work decomposition (round 2): a warp takes a (token, head segment) unit and walks the segment's heads four at
+// a time (one head per 8-lane group).  Everything that depends on the token only -- position, the 16 cos/sin
+// values a lane needs, the cache slot, the three row base pointers -- is fetched ONCE per unit instead of once
+// per row (the old row-major walk paid a division by H, a position load and four 16-byte cos/sin loads per
+// (token, head) row: about as many instructions as the arithmetic itself), and the row type (q / k / v) is two
+// compares on the head index.  Within a unit the loads of the next four heads are in flight while the current
+// four are normalised, rotated and stored.  `nseg` segments per token keep the machine full at decode sizes.
+#ifndef NR_BLOCKS
+#define NR_BLOCKS 4
+#endif
+struct RowData { int4 lo, hi; };                   // elements [8s, 8s+8) and [64+8s, 64+8s+8) of a row
 
 template <bool STORE>
-__device__ __forceinline__ RowLoad load_row(uint32_t row, uint32_t total_rows, uint32_t H, uint32_t Hq, uint32_t Hkv, int sub,
-                                            const __nv_bfloat16* q, int64_t q_token_stride, const __nv_bfloat16* k, int64_t k_token_stride,
-                                            const int64_t* positions, const float* cos_sin, __nv_bfloat16* q_out, __nv_bfloat16* k_out,
-                                            const KvStoreArgs& st) {
-    RowLoad r;
-    r.live = row < total_rows;                     // dead lanes still take part in the shuffles
-    const uint32_t tok = r.live ? row / H : 0;
-    const uint32_t h = r.live ? row - tok * H : 0;
-    r.is_q = h < Hq;
-    r.is_v = STORE && h >= Hq + Hkv;
-    const __nv_bfloat16* src = r.is_q ? q + (int64_t)tok * q_token_stride + (int64_t)h * B200_HD
-                             : r.is_v ? st.v + (int64_t)tok * st.v_token_stride + (int64_t)(h - Hq - Hkv) * B200_HD
-                                      : k + (int64_t)tok * k_token_stride + (int64_t)(h - Hq) * B200_HD;
-    r.dst = r.is_q ? q_out + ((int64_t)tok * Hq + h) * B200_HD
-                   : (k_out != nullptr && !r.is_v ? k_out + ((int64_t)tok * Hkv + (h - Hq)) * B200_HD : nullptr);
-    r.lo = r.hi = make_int4(0, 0, 0, 0);
-    r.cache_dst = nullptr;
-    r.cs = cos_sin;
-    if (r.live) {
-        r.lo = ld_nc_v4(src + 8 * sub);
-        r.hi = ld_nc_v4(src + 64 + 8 * sub);
-        if (!r.is_v) r.cs = cos_sin + __ldg(positions + tok) * B200_HD + 8 * sub;       // [cos(64) | sin(64)]
-        if (STORE && !r.is_q) {
-            const int32_t slot = __ldg(st.slot_mapping + tok);
-            if (slot >= 0)
-                r.cache_dst = (r.is_v ? st.v_cache + (int64_t)(h - Hq - Hkv) * B200_HD : st.k_cache + (int64_t)(h - Hq) * B200_HD)
-                              + (int64_t)slot * Hkv * B200_HD;
-        }
-    }
-    return r;
-}
-
-template <bool STORE>
-__global__ void __launch_bounds__(256) qk_norm_rope_kernel(
+__global__ void __launch_bounds__(256, NR_BLOCKS) qk_norm_rope_kernel(
     const __nv_bfloat16* __restrict__ q, int64_t q_token_stride,
     const __nv_bfloat16* __restrict__ k, int64_t k_token_stride,
     const int64_t* __restrict__ positions, const float* __restrict__ cos_sin,
     const __nv_bfloat16* __restrict__ q_weight, const __nv_bfloat16* __restrict__ k_weight, float eps,
     __nv_bfloat16* __restrict__ q_out, __nv_bfloat16* __restrict__ k_out,
-    uint32_t total_rows, uint32_t Hq, uint32_t Hkv, const KvStoreArgs st) {
-    const int sub = threadIdx.x & 7;
+    uint32_t T, uint32_t Hq, uint32_t Hkv, uint32_t nseg, uint32_t hps, const KvStoreArgs st) {
+    const int sub = threadIdx.x & 7, grp = (threadIdx.x >> 3) & 3;
     const uint32_t H = STORE ? Hq + 2 * Hkv : Hq + Hkv;
     const bool has_w = q_weight != nullptr;                    // both weights or neither (checked at the ABI)
-    const uint32_t group = (blockIdx.x * 256u + threadIdx.x) >> 3;            // 8-lane row group of this thread
-    const uint32_t groups = gridDim.x * 32u;
-    // Software pipeline over this group's rows (group, group + groups, ...): the loads of row n+1 are in flight
-    // while row n is normalised, rotated and stored.  Every lane of a warp runs the same number of rounds.
-    RowLoad cur = load_row<STORE>(group, total_rows, H, Hq, Hkv, sub, q, q_token_stride, k, k_token_stride, positions, cos_sin, q_out, k_out, st);
-    for (uint32_t base = 0; base < total_rows; base += groups) {
-        const RowLoad nxt = load_row<STORE>(group + base + groups, base + groups < total_rows ? total_rows : 0u, H, Hq, Hkv, sub,
-                                            q, q_token_stride, k, k_token_stride, positions, cos_sin, q_out, k_out, st);
-        if (STORE && cur.is_v && cur.cache_dst != nullptr) {       // v is copied untouched
-            st_v4(cur.cache_dst + 8 * sub, cur.lo);
-            st_v4(cur.cache_dst + 64 + 8 * sub, cur.hi);
+    const uint32_t warp_global = (blockIdx.x * 256u + threadIdx.x) >> 5, n_warps = gridDim.x * 8u;
+    const uint32_t units = T * nseg;
+
+    for (uint32_t unit = warp_global; unit < units; unit += n_warps) {
+        const uint32_t tok = unit / nseg, seg = unit - tok * nseg;
+        const uint32_t h_begin = seg * hps, h_end = min(H, h_begin + hps);
+        // ---- per-token state ----------------------------------------------------------------------
+        const float* cs = cos_sin + __ldg(positions + tok) * B200_HD + 8 * sub;          // [cos(64) | sin(64)]
+        const float4 c0 = __ldg(reinterpret_cast<const float4*>(cs)), c1 = __ldg(reinterpret_cast<const float4*>(cs + 4));
+        const float4 s0 = __ldg(reinterpret_cast<const float4*>(cs + 64)), s1 = __ldg(reinterpret_cast<const float4*>(cs + 68));
+        const float c[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+        const float s[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+        const __nv_bfloat16* q_tok = q + (int64_t)tok * q_token_stride + 8 * sub;
+        const __nv_bfloat16* k_tok = k + (int64_t)tok * k_token_stride + 8 * sub;
+        const __nv_bfloat16* v_tok = STORE ? st.v + (int64_t)tok * st.v_token_stride + 8 * sub : nullptr;
+        __nv_bfloat16* qo_tok = q_out + (int64_t)tok * Hq * B200_HD + 8 * sub;
+        __nv_bfloat16* ko_tok = k_out != nullptr ? k_out + (int64_t)tok * Hkv * B200_HD + 8 * sub : nullptr;
+        int64_t cache_off = -1;                                     // element offset of this token's slot, -1: no cache write
+        if (STORE) {
+            const int32_t slot = __ldg(st.slot_mapping + tok);
+            if (slot >= 0) cache_off = (int64_t)slot * Hkv * B200_HD + 8 * sub;
         }
-        const uint32_t lo_u[4] = {(uint32_t)cur.lo.x, (uint32_t)cur.lo.y, (uint32_t)cur.lo.z, (uint32_t)cur.lo.w};
-        const uint32_t hi_u[4] = {(uint32_t)cur.hi.x, (uint32_t)cur.hi.y, (uint32_t)cur.hi.z, (uint32_t)cur.hi.w};
-        float x1[8], x2[8];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            x1[2 * j] = bf_lo(lo_u[j]); x1[2 * j + 1] = bf_hi(lo_u[j]);
-            x2[2 * j] = bf_lo(hi_u[j]); x2[2 * j + 1] = bf_hi(hi_u[j]);
-        }
-        if (has_w) {                                           // uniform: nullptr => rotation only (RotaryEmbedding.forward)
-            float ss = 0.f;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) ss += x1[j] * x1[j] + x2[j] * x2[j];
-#pragma unroll
-            for (int o = 4; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-            const float rstd = rsqrtf(__fadd_rn(ss * (1.0f / B200_HD), eps));
-            const __nv_bfloat16* w = cur.is_q ? q_weight : k_weight;           // 2 x 16 bytes, L1-resident
-            const int4 wl4 = __ldg(reinterpret_cast<const int4*>(w + 8 * sub));
-            const int4 wh4 = __ldg(reinterpret_cast<const int4*>(w + 64 + 8 * sub));
-            const uint32_t wl_u[4] = {(uint32_t)wl4.x, (uint32_t)wl4.y, (uint32_t)wl4.z, (uint32_t)wl4.w};
-            const uint32_t wh_u[4] = {(uint32_t)wh4.x, (uint32_t)wh4.y, (uint32_t)wh4.z, (uint32_t)wh4.w};
-            // bf16(x * rstd) then bf16(that * w): two roundings, as in the reference.  The first is one packed F2FP
-            // per pair; the second is ONE packed bf16 multiply: the product of two bf16 values is exact in fp32, so
-            // HMUL2.BF16 (fp32 product, one round-to-nearest-even) returns the bits of bf16(float(y) * float(w)).
+        auto src_of = [&](uint32_t h) -> const __nv_bfloat16* {
+            return h < Hq ? q_tok + h * B200_HD : (STORE && h >= Hq + Hkv ? v_tok + (h - Hq - Hkv) * B200_HD : k_tok + (h - Hq) * B200_HD);
+        };
+        auto load = [&](uint32_t h) {
+            RowData r;
+            r.lo = r.hi = make_int4(0, 0, 0, 0);
+            if (h < h_end) { const __nv_bfloat16* src = src_of(h); r.lo = ld_nc_v4(src); r.hi = ld_nc_v4(src + 64); }
+            return r;
+        };
+        RowData cur = load(h_begin + grp), nxt = load(h_begin + grp + 4);
+        for (uint32_t hb = h_begin; hb < h_end; hb += 4) {           // uniform trip count for the whole warp
+            const uint32_t h = hb + grp;
+            const RowData nxt2 = load(h + 8);                        // two head-quads (2 KB per warp) in flight
+            const bool live = h < h_end, is_q = h < Hq, is_v = STORE && h >= Hq + Hkv;
+            if (STORE && is_v && live && cache_off >= 0) {           // v is copied untouched
+                __nv_bfloat16* dst = st.v_cache + cache_off + (int64_t)(h - Hq - Hkv) * B200_HD;
+                st_v4(dst, cur.lo);
+                st_v4(dst + 64, cur.hi);
+            }
+            const uint32_t lo_u[4] = {(uint32_t)cur.lo.x, (uint32_t)cur.lo.y, (uint32_t)cur.lo.z, (uint32_t)cur.lo.w};
+            const uint32_t hi_u[4] = {(uint32_t)cur.hi.x, (uint32_t)cur.hi.y, (uint32_t)cur.hi.z, (uint32_t)cur.hi.w};
+            float x1[8], x2[8];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                const uint32_t a = pack_bf16x2(__fmul_rn(x1[2 * j], rstd), __fmul_rn(x1[2 * j + 1], rstd));
-                const uint32_t b = pack_bf16x2(__fmul_rn(x2[2 * j], rstd), __fmul_rn(x2[2 * j + 1], rstd));
-                const __nv_bfloat162 c2 = __hmul2(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&wl_u[j]));
-                const __nv_bfloat162 d2 = __hmul2(*reinterpret_cast<const __nv_bfloat162*>(&b), *reinterpret_cast<const __nv_bfloat162*>(&wh_u[j]));
-                const uint32_t c = *reinterpret_cast<const uint32_t*>(&c2), d = *reinterpret_cast<const uint32_t*>(&d2);
-                x1[2 * j] = bf_lo(c); x1[2 * j + 1] = bf_hi(c);
-                x2[2 * j] = bf_lo(d); x2[2 * j + 1] = bf_hi(d);
+                x1[2 * j] = bf_lo(lo_u[j]); x1[2 * j + 1] = bf_hi(lo_u[j]);
+                x2[2 * j] = bf_lo(hi_u[j]); x2[2 * j + 1] = bf_hi(hi_u[j]);
             }
-        }
-        if (cur.live && !cur.is_v) {
-            const float4 c0 = __ldg(reinterpret_cast<const float4*>(cur.cs)), c1 = __ldg(reinterpret_cast<const float4*>(cur.cs + 4));
-            const float4 s0 = __ldg(reinterpret_cast<const float4*>(cur.cs + 64)), s1 = __ldg(reinterpret_cast<const float4*>(cur.cs + 68));
-            const float c[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
-            const float s[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
-            uint32_t y1[4], y2[4];
+            if (has_w) {                                           // uniform: nullptr => rotation only (RotaryEmbedding.forward)
+                float ss = 0.f;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                // y1 = x1*cos - x2*sin ; y2 = x2*cos + x1*sin  (un-fused, matching eager fp32)
-                const int a = 2 * j, b = 2 * j + 1;
-                y1[j] = pack_bf16x2(__fsub_rn(__fmul_rn(x1[a], c[a]), __fmul_rn(x2[a], s[a])),
-                                    __fsub_rn(__fmul_rn(x1[b], c[b]), __fmul_rn(x2[b], s[b])));
-                y2[j] = pack_bf16x2(__fadd_rn(__fmul_rn(x2[a], c[a]), __fmul_rn(x1[a], s[a])),
-                                    __fadd_rn(__fmul_rn(x2[b], c[b]), __fmul_rn(x1[b], s[b])));
+                for (int j = 0; j < 8; ++j) ss += x1[j] * x1[j] + x2[j] * x2[j];
+#pragma unroll
+                for (int o = 4; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+                const float rstd = rsqrtf(__fadd_rn(ss * (1.0f / B200_HD), eps));
+                // bf16(x * rstd) then bf16(that * w): two roundings, as in the reference.  The first is one packed F2FP
+                // per pair; the second is ONE packed bf16 multiply: the product of two bf16 values is exact in fp32, so
+                // HMUL2.BF16 (fp32 product, one round-to-nearest-even) returns the bits of bf16(float(y) * float(w)).
+                const __nv_bfloat16* w = (is_q ? q_weight : k_weight) + 8 * sub;        // 2 x 16 bytes, L1-resident
+                const int4 wl4 = __ldg(reinterpret_cast<const int4*>(w)), wh4 = __ldg(reinterpret_cast<const int4*>(w + 64));
+                const uint32_t wl_u[4] = {(uint32_t)wl4.x, (uint32_t)wl4.y, (uint32_t)wl4.z, (uint32_t)wl4.w};
+                const uint32_t wh_u[4] = {(uint32_t)wh4.x, (uint32_t)wh4.y, (uint32_t)wh4.z, (uint32_t)wh4.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const uint32_t wl = wl_u[j], wh = wh_u[j];
+                    const uint32_t a = pack_bf16x2(__fmul_rn(x1[2 * j], rstd), __fmul_rn(x1[2 * j + 1], rstd));
+                    const uint32_t b = pack_bf16x2(__fmul_rn(x2[2 * j], rstd), __fmul_rn(x2[2 * j + 1], rstd));
+                    const __nv_bfloat162 c2 = __hmul2(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&wl));
+                    const __nv_bfloat162 d2 = __hmul2(*reinterpret_cast<const __nv_bfloat162*>(&b), *reinterpret_cast<const __nv_bfloat162*>(&wh));
+                    const uint32_t cc = *reinterpret_cast<const uint32_t*>(&c2), dd = *reinterpret_cast<const uint32_t*>(&d2);
+                    x1[2 * j] = bf_lo(cc); x1[2 * j + 1] = bf_hi(cc);
+                    x2[2 * j] = bf_lo(dd); x2[2 * j + 1] = bf_hi(dd);
+                }
             }
-            const int4 o_lo = make_int4(y1[0], y1[1], y1[2], y1[3]), o_hi = make_int4(y2[0], y2[1], y2[2], y2[3]);
-            if (cur.dst != nullptr) {
-                st_v4(cur.dst + 8 * sub, o_lo);
-                st_v4(cur.dst + 64 + 8 * sub, o_hi);
+            if (live && !is_v) {
+                uint32_t y1[4], y2[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    // y1 = x1*cos - x2*sin ; y2 = x2*cos + x1*sin  (un-fused, matching eager fp32)
+                    const int a = 2 * j, b = 2 * j + 1;
+                    y1[j] = pack_bf16x2(__fsub_rn(__fmul_rn(x1[a], c[a]), __fmul_rn(x2[a], s[a])),
+                                        __fsub_rn(__fmul_rn(x1[b], c[b]), __fmul_rn(x2[b], s[b])));
+                    y2[j] = pack_bf16x2(__fadd_rn(__fmul_rn(x2[a], c[a]), __fmul_rn(x1[a], s[a])),
+                                        __fadd_rn(__fmul_rn(x2[b], c[b]), __fmul_rn(x1[b], s[b])));
+                }
+                const int4 o_lo = make_int4(y1[0], y1[1], y1[2], y1[3]), o_hi = make_int4(y2[0], y2[1], y2[2], y2[3]);
+                __nv_bfloat16* dst = is_q ? qo_tok + h * B200_HD : (ko_tok != nullptr ? ko_tok + (h - Hq) * B200_HD : nullptr);
+                if (dst != nullptr) {
+                    st_v4(dst, o_lo);
+                    st_v4(dst + 64, o_hi);
+                }
+                if (STORE && !is_q && cache_off >= 0) {
+                    __nv_bfloat16* cd = st.k_cache + cache_off + (int64_t)(h - Hq) * B200_HD;
+                    st_v4(cd, o_lo);
+                    st_v4(cd + 64, o_hi);
+                }
             }
-            if (STORE && cur.cache_dst != nullptr) {
-                st_v4(cur.cache_dst + 8 * sub, o_lo);
-                st_v4(cur.cache_dst + 64 + 8 * sub, o_hi);
-            }
+            cur = nxt; nxt = nxt2;
         }
-        cur = nxt;
     }
 }
 
@@ -337,13 +337,35 @@ int launch_kv_scatter_generic(const void* key, const void* value, int64_t key_ro
     return launch_kv_scatter(key, value, key_row_stride, value_row_stride, k_cache, v_cache, slot_mapping, T, Hkv, D, stream);
 }
 
-// rows are spread over at most 8 CTAs per SM (the grid-stride loop takes the rest): enough CTAs to fill
-// the machine, few enough that a 16k-token prefill is not 25k tiny CTAs
-static inline int norm_rope_grid(int64_t rows) {
-    int64_t blocks = (rows + 31) / 32;                            // 32 rows per CTA per round
-    const int64_t cap = (int64_t)sm_count() * 8;
+// Units = (token, head segment).  One segment per token when there are enough tokens to fill the machine (the whole
+// cos/sin row, position and slot are then fetched once per token); at decode sizes the heads of a token are split into
+// up to ceil(H/4) segments so that ~8 warps per SM sub-partition still have work.
+struct NormRopeShape { uint32_t nseg, hps; int grid; };
+template <bool STORE>
+static inline int norm_rope_resident_blocks() {                  // CTAs of this kernel an SM holds (per device, cached)
+    static int cached[64] = {0};
+    const int dev = current_device();
+    if (dev < 0 || dev >= 64) return 2;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, qk_norm_rope_kernel<STORE>, 256, 0) != cudaSuccess || n < 1) n = 2;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+static inline NormRopeShape norm_rope_shape(int64_t T, int H, int resident) {
+    const int64_t want_units = (int64_t)sm_count() * 32 * 2;      // two units per resident warp
+    int64_t nseg = T > 0 ? (want_units + T - 1) / T : 1;
+    const int max_seg = (H + 3) / 4;
+    if (nseg < 1) nseg = 1;
+    if (nseg > max_seg) nseg = max_seg;
+    int hps = (int)(((H + nseg - 1) / nseg + 3) / 4 * 4);
+    nseg = (H + hps - 1) / hps;
+    const int64_t units = T * nseg;
+    int64_t blocks = (units + 7) / 8;                              // 8 warps per CTA, one unit per warp per round
+    const int64_t cap = (int64_t)sm_count() * resident;           // exactly one wave: the grid-stride loop takes the rest
     if (blocks > cap) blocks = cap;
-    return (int)(blocks < 1 ? 1 : blocks);
+    return {(uint32_t)nseg, (uint32_t)hps, (int)(blocks < 1 ? 1 : blocks)};
 }
 
 int launch_qk_norm_rope(const void* q, int64_t q_token_stride, const void* k, int64_t k_token_stride,
@@ -351,10 +373,12 @@ int launch_qk_norm_rope(const void* q, int64_t q_token_stride, const void* k, in
                         void* q_out, void* k_out, int32_t T, int32_t Hq, int32_t Hkv, cudaStream_t stream) {
     const int64_t rows = (int64_t)T * (Hq + Hkv);
     if (rows >= (int64_t)1 << 31) return -5;
-    qk_norm_rope_kernel<false><<<norm_rope_grid(rows), 256, 0, stream>>>(
+    if (T == 0) return 0;
+    const NormRopeShape sh = norm_rope_shape(T, Hq + Hkv, norm_rope_resident_blocks<false>());
+    qk_norm_rope_kernel<false><<<sh.grid, 256, 0, stream>>>(
         (const __nv_bfloat16*)q, q_token_stride, (const __nv_bfloat16*)k, k_token_stride, positions, cos_sin,
         (const __nv_bfloat16*)qw, (const __nv_bfloat16*)kw, eps, (__nv_bfloat16*)q_out, (__nv_bfloat16*)k_out,
-        (uint32_t)rows, (uint32_t)Hq, (uint32_t)Hkv, KvStoreArgs{});
+        (uint32_t)T, (uint32_t)Hq, (uint32_t)Hkv, sh.nseg, sh.hps, KvStoreArgs{});
     return (int)cudaGetLastError();
 }
 
@@ -365,13 +389,15 @@ int launch_qk_norm_rope_store(const void* q, int64_t q_token_stride, const void*
                               int32_t T, int32_t Hq, int32_t Hkv, cudaStream_t stream) {
     const int64_t rows = (int64_t)T * (Hq + 2 * Hkv);
     if (rows >= (int64_t)1 << 31) return -5;
+    if (T == 0) return 0;
     KvStoreArgs st;
     st.v = (const __nv_bfloat16*)v; st.v_token_stride = v_token_stride;
     st.k_cache = (__nv_bfloat16*)k_cache; st.v_cache = (__nv_bfloat16*)v_cache; st.slot_mapping = slot_mapping;
-    qk_norm_rope_kernel<true><<<norm_rope_grid(rows), 256, 0, stream>>>(
+    const NormRopeShape sh = norm_rope_shape(T, Hq + 2 * Hkv, norm_rope_resident_blocks<true>());
+    qk_norm_rope_kernel<true><<<sh.grid, 256, 0, stream>>>(
         (const __nv_bfloat16*)q, q_token_stride, (const __nv_bfloat16*)k, k_token_stride, positions, cos_sin,
         (const __nv_bfloat16*)qw, (const __nv_bfloat16*)kw, eps, (__nv_bfloat16*)q_out, (__nv_bfloat16*)k_out,
-        (uint32_t)rows, (uint32_t)Hq, (uint32_t)Hkv, st);
+        (uint32_t)T, (uint32_t)Hq, (uint32_t)Hkv, sh.nseg, sh.hps, st);
     return (int)cudaGetLastError();
 }
 
