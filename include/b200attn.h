@@ -105,10 +105,11 @@ int b200_nvls_allreduce_add_rmsnorm(void* comm, const void* x, void* residual, c
 int b200_nvls_status(void* comm, int32_t* status_out);
 int b200_nvls_destroy(void* comm);
 
-/* Debug/profiling aid (no reference counterpart): while `dev_buf` (zeroed int64[4][max_tiles][8] in
+/* Debug/profiling aid (no reference counterpart): while `dev_buf` (zeroed int64[6][max_tiles][8] in
  * device memory) is non-NULL, b200_attn_prefill_planned runs an instrumented build whose CTA 0 stamps
  * clock64 at the phase boundaries of its first `max_tiles` tiles (rows 0/1: softmax warpgroups: wait,
- * S ready, S loaded, max done, exp done, P published; rows 2/3: MMA issuer: wait P, P seen, issued).
+ * S ready, S loaded, max done, exp done, P published; rows 2/3: MMA issuer: wait P, P seen, issued,
+ * unit boundaries; rows 4/5: epilogue phases of a unit's last tile).
  * Pass NULL to return to the product kernel.  tools/trace_prefill.py reads it. */
 int b200_debug_prefill_trace(void* dev_buf, int max_tiles);
 
