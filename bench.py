@@ -245,7 +245,27 @@ def run_ours(args):
         step_e2e()
     sampler = ClockSampler(local)
     sampler.start()
-    ms_total = timed(step_resident, args.steps)
+    # `value`: the step replayed from a CUDA graph -- how the engine runs this very call (ModelRunner.capture_cudagraph /
+    # run_model replay, model_runner.py:568-600,640-715: graph-form decode, row a6/a13); the eager launches of the same
+    # step are timed next to it and reported as `eager_ms_per_step`.
+    launch_mode = "cuda-graph replay (ModelRunner's decode form)"
+    try:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            step_resident()
+        torch.cuda.current_stream().wait_stream(side)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            step_resident()
+        for _ in range(3):
+            graph.replay()
+        step_timed = graph.replay
+    except Exception as e:                                      # noqa: BLE001
+        launch_mode = f"eager launches (graph capture failed: {type(e).__name__})"
+        step_timed = step_resident
+    ms_eager = timed(step_resident, args.steps)
+    ms_total = timed(step_timed, args.steps)
     ms_e2e = timed(step_e2e, args.steps)
     clocks = sampler.finish()                                  # covers both timed regions (resident + e2e)
 
@@ -305,6 +325,7 @@ def run_ours(args):
                    "step": "Attention.forward = kv_scatter + paged decode (split merge inside the decode launch)",
                    "num_splits": num_splits,
                    "l2": "inputs larger than L2 (K/V working set %.2f GB per GPU vs 126 MB L2)" % (dec_b / 1e9)},
+        "launch": launch_mode, "eager_ms_per_step": round(ms_eager / args.steps, 4),
         "e2e": {"value": round(e2e_value, 1), "unit": "GB/s", "h2d_bytes_per_step": h2d * world,
                 "d2h_bytes_per_step": d2h * world, "ms_per_step": round(ms_e2e / args.steps, 4)},
         "gpu_launches": launches_per_step * args.steps,
