@@ -6,6 +6,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <math.h>
 #include "launch.h"
 
 namespace b200 {
@@ -88,26 +89,34 @@ int b200_kv_scatter(const void* key, const void* value, int64_t key_row_stride, 
 }
 
 // Host-only heuristic (static under CUDA graphs, like flash-attn's num_splits which is fixed at
-// capture time): smallest split count whose grid fills >= 90 % of its last wave, never finer
+// capture time): the split count that minimises a small cost model of the launch, never finer
 // than one page per split.
 int b200_decode_plan(int32_t batch, int32_t num_kv_heads, int32_t max_context_len) {
     if (batch <= 0 || num_kv_heads <= 0) return 1;
     const char* env = getenv("B200ATTN_DECODE_SPLITS");
     if (env && atoi(env) > 0) return atoi(env);
-    const int64_t slots = (int64_t)sm_count() * 2;               // 2 resident CTAs per SM
-    const int64_t items = (int64_t)batch * num_kv_heads;
-    if (items >= slots * 4) return 1;
-    int cap = (max_context_len + 255) / 256;
+    // Cost model fitted to the (CTA shape x split count) sweep of round 2 (profiles/r2_sweep_decode_tp.txt), in bytes
+    // moved at HBM speed.  The kernel is HBM-bound, so a partly filled last wave costs nothing while it still holds
+    // enough CTAs to saturate HBM: cfg3 at the TP8 heads (512 items on 296 slots) runs 9 % faster unsplit than with the
+    // 4 splits that "fill the last wave".  What does cost: (a) a CTA on its own streams at ~1/100 of HBM bandwidth
+    // (64 GB/s measured), so a sparse wave lasts at least 100 x the bytes of one CTA; (b) ~3 us per wave of fixed work
+    // (prologue latency, cross-warp merge, partial write + ticket), i.e. ~20 MB at HBM speed; (c) below.
+    const double slots = (double)sm_count() * 2;                 // 2 resident CTAs per SM
+    const double items = (double)batch * num_kv_heads;
+    const double row_bytes = (double)(max_context_len > 0 ? max_context_len : 1) * 512.0;   // K + V of one kv head
+    int cap = (max_context_len + 255) / 256;                     // never finer than one page per split
     if (cap < 1) cap = 1;
     if (cap > 64) cap = 64;
     int best = 1;
-    double best_eff = 0.0;
+    double best_cost = 0.0;
     for (int s = 1; s <= cap; ++s) {
-        const int64_t ctas = items * s;
-        const int64_t waves = (ctas + slots - 1) / slots;
-        const double eff = (double)ctas / (double)(waves * slots);
-        if (eff > best_eff + 1e-9) { best_eff = eff; best = s; }
-        if (eff >= 0.90) { best = s; break; }
+        const double ctas = items * s, per = row_bytes / s;
+        const double full = floor(ctas / slots), tail = ctas - full * slots;
+        double cost = full * slots * per + (full + (tail > 0 ? 1 : 0)) * 20.0e6;
+        if (tail > 0) cost += per * (tail > 100.0 ? tail : 100.0);
+        if (s > 1) cost += ctas * 4096.0 + 5.0e6;                // partial O/LSE round trip + the last arriver's merge
+        if (ctas < slots) cost *= 1.0 + 0.04 * (1.0 - ctas / slots);   // (c) a machine that is not full streams a few % slower
+        if (s == 1 || cost < best_cost * 0.995) { best_cost = cost; best = s; }
     }
     return best;
 }

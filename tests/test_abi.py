@@ -61,6 +61,13 @@ def test_decode_plan_is_static_and_bounded(lib):
     s = lib.b200_decode_plan(64, 1, 32832)                   # cfg5 decode: few items, long context
     assert 2 <= s <= 64
     assert lib.b200_decode_plan(1, 8, 300) <= 2              # never finer than one page per split
+    # round 2 (profiles/r2_sweep_decode_tp.txt): an HBM-bound launch with at least one full wave of items is NOT split to
+    # "fill the last wave" -- cfg3 at the TP2/TP4/TP8 heads runs unsplit (TP8: 158 us unsplit vs 172 us with 4 splits)
+    for hkv in (4, 2, 1):
+        assert lib.b200_decode_plan(512, hkv, 4096) == 1
+    assert lib.b200_decode_plan(256, 2, 1280) == 1
+    assert lib.b200_decode_plan(1, 8, 4096) >= 8             # a lone sequence is spread over the machine
+    assert lib.b200_decode_plan(512, 1, 4096) == lib.b200_decode_plan(512, 1, 4096)   # pure function of its arguments
     assert lib.b200_decode_workspace_bytes(4, 32, 1) == 0
     assert lib.b200_decode_workspace_bytes(4, 32, 3) == 64 * 1024 + 4 * 3 * 32 * 129 * 4   # tickets + partial O + LSE
 

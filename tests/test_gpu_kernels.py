@@ -236,7 +236,7 @@ def test_planned_paged_mixed_vs_oracle(ops, Hq, Hkv):
     assert maxerr(got, want) <= ATOL
 
 
-@pytest.mark.parametrize("Hq,Hkv", [(16, 8), (8, 1)])
+@pytest.mark.parametrize("Hq,Hkv", [(16, 8), (8, 1), (2, 1), (1, 1), (5, 1), (6, 2)])   # units per item 8, 4, 1, 1, 5, 3
 def test_planned_unpaged_vs_oracle(ops, Hq, Hkv):
     lens = [128, 1, 63, 64, 65, 300, 7, 1, 600]
     g = torch.Generator().manual_seed(9)
