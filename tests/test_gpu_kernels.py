@@ -725,3 +725,34 @@ def test_decode_full_size_cfg3_tp_shapes(ops, Hq, Hkv):
     want = oracle.attn_decode(q[idx.cuda()].cpu(), kc[uniq.cuda().long()].cpu(), vc[uniq.cuda().long()].cpu(),
                               lens[idx.cuda()].cpu(), inv.to(torch.int32), SCALE)
     assert maxerr(out_auto[idx.cuda()], want) <= ATOL
+
+
+@pytest.mark.parametrize("env", [{"B200ATTN_PREFILL_WGS": "2"}, {"B200ATTN_PREFILL_EMU": "1"}, {"B200ATTN_PREFILL_WGS": "2", "B200ATTN_PREFILL_EMU": "2"},
+                                 {"B200ATTN_DECODE_FUSED_REDUCE": "0", "B200ATTN_DECODE_SPLITS": "3"}])
+def test_measured_and_not_adopted_variants_still_match_the_oracle(env):
+    """The A/B knobs kept in the shipped library (two softmax warpgroups per query tile, polynomial exp2, the separate
+    reduce launch) are read once per process, so each runs in a subprocess: a mixed paged batch (prefill rows through the
+    persistent kernel, 1-token rows through the decode kernel) against the oracle."""
+    import subprocess
+    import sys
+    code = r'''
+import sys, torch
+sys.path[:0] = [%r, %r, %r]
+import oracle
+from helpers import make_paged_case
+from b200attn import ops
+lens_q = [300, 1, 128, 1, 700, 64, 1, 257]
+lens_k = [300, 900, 640, 17, 700, 1000, 256, 257]
+for Hq, Hkv in ((16, 8), (8, 1), (5, 1)):
+    c = make_paged_case(31 + Hq, lens_q, lens_k, Hq, Hkv)
+    want = oracle.attn_varlen(c["q"], c["k_cache"], c["v_cache"], c["cu_seqlens_q"], c["cu_seqlens_k"], 128 ** -0.5, c["block_tables"])
+    d = lambda t: t.cuda()
+    got = ops.attn_varlen_planned(d(c["q"]), d(c["k_cache"]), d(c["v_cache"]), d(c["cu_seqlens_q"]), d(c["cu_seqlens_k"]),
+                                  c["max_seqlen_q"], c["max_seqlen_k"], 128 ** -0.5, block_table=d(c["block_tables"]))
+    err = (got.float().cpu() - want.float()).abs().max().item()
+    assert torch.isfinite(got.float()).all() and err <= 2e-2, (Hq, Hkv, err)
+print("ok")
+''' % (os.path.dirname(os.path.abspath(__file__)), os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+       os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "nano-vllm-v1_b200"))
+    r = subprocess.run([sys.executable, "-c", code], env={**os.environ, **env}, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]

@@ -13,7 +13,8 @@ import torch
 from b200attn import ops
 D, PAGE = 128, 256
 cases = {"cfg3_tp8": (512, 4096, 4, 1), "cfg3_tp4": (512, 4096, 8, 2), "cfg3_tp2": (512, 4096, 16, 4), "cfg5_tp8": (64, 32832, 8, 1),
-         "cfg2": (256, 384, 16, 8)}
+         "cfg2": (256, 384, 16, 8), "bs256_ctx256": (256, 256, 32, 8), "bs256_ctx1280": (256, 1280, 32, 8), "bs64_ctx2048": (64, 2048, 32, 8),
+         "bs256_ctx1280_tp4": (256, 1280, 8, 2), "cfg3_tp1": (512, 4096, 32, 8)}
 out = {}
 for name in sys.argv[1:] or list(cases):
     B, ctx, Hq, Hkv = cases[name]
