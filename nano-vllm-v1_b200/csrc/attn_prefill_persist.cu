@@ -216,6 +216,9 @@ constexpr int ps_threads(int wgs) { return wgs == 2 ? 640 : 384; }
 #define PS_W1_LOW 72
 #define PS_W1_HIGH 216
 #endif
+#ifndef PS_P_HALF
+#define PS_P_HALF 1      // publish the first 64 columns of P early (build knob; 0: one publication per tile)
+#endif
 #ifndef PS_CROSS_UNIT
 #define PS_CROSS_UNIT 0
 #endif
@@ -411,14 +414,17 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
                         for (int t = 0; t < 2; ++t) {
                             if (j < u.nt(t)) {
                                 stamp(t, p_cnt[t], 0);
-                                mbar_wait(p_half(t), p_cnt[t] & 1u);
-                                tc_fence_after();
-                                issue_pv(t, st, j == 0, 0);
+                                if (PS_P_HALF || WGS == 2) {
+                                    mbar_wait(p_half(t), p_cnt[t] & 1u);
+                                    tc_fence_after();
+                                    issue_pv(t, st, j == 0, 0);
+                                }
                                 stamp(t, p_cnt[t], 3);
                                 mbar_wait(p_full(t), p_cnt[t] & 1u);
                                 stamp(t, p_cnt[t], 1);
                                 ++p_cnt[t];
                                 tc_fence_after();
+                                if (!(PS_P_HALF || WGS == 2)) issue_pv(t, st, j == 0, 0);
                                 issue_pv(t, st, false, 1);
                                 if (j + 1 < u.nt(t)) {
                                     issue_qk(t, (it + 1) % S);
@@ -756,7 +762,7 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
                             pk[k & 15] = cvt_bf16x2(p0, p1);
                             if ((k & 15) == 15) tmem_st16(tS + (k >> 4) * 16, pk);
                         }
-                        if (i == HALF_AT) {                         // stores of columns 0..63 were issued 6 pairs ago
+                        if (PS_P_HALF && i == HALF_AT) {                         // stores of columns 0..63 were issued 6 pairs ago
                             tmem_wait_st();
                             tc_fence_before();
                             mbar_arrive(p_half(t));
