@@ -24,6 +24,15 @@ print("no flush, idle before      ", t(lambda: None))
 print("read sweep 256MB (max)     ", t(lambda: flush.max()))
 print("write sweep 256MB (zero_)  ", t(lambda: flush.zero_()))
 print("spin kernel 100us no L2    ", t(lambda: torch.cuda._sleep(200000)))
+import time
+def sl(ms):
+    def f():
+        time.sleep(ms / 1e3); flush.max()
+    return f
+print("20 ms sleep + read sweep   ", t(sl(20)))
+print("2 ms sleep + read sweep    ", t(sl(2)))
+print("read sweep only            ", t(lambda: flush.max()))
+print("200 ms sleep + read sweep  ", t(sl(200), 8))
 print("no flush again             ", t(lambda: None))
 # two launches back to back, time the second
 def t2(n=15):
