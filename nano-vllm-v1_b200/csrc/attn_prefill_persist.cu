@@ -26,11 +26,15 @@ struct PersistParams {
     const int32_t* cu_q; const int32_t* cu_k; const int32_t* block_tables; int32_t bt_row_stride;
     __nv_bfloat16* out; int64_t out_token_stride;
     int32_t Hq, G, pair_heads; float scale_log2;
+    int32_t pack_ok;                               // short query tiles may pack two q heads per 128-row tile (see Unit::pack)
     uint32_t per_item, per_item_magic, g_magic16;   // units per item; ceil(2^32 / per_item); ceil(2^16 / G): exact division by multiply-high
     const int32_t* plan; const int32_t* items;
     long long* trace; int32_t trace_tiles;      // TRACE builds only: clock64 stamps of CTA 0 (b200_debug_prefill_trace)
 };
 
+#ifndef PS_PACK
+#define PS_PACK 1        // two q heads per 128-row tile for query tiles with <= 64 valid rows (build knob)
+#endif
 constexpr int PREFILL_EMU_DEFAULT = 0;
 constexpr int PREFILL_WGS_DEFAULT = 1;
 
@@ -57,8 +61,12 @@ struct PsSmem {
 // One work unit = two 128-row query tiles that share one stream of K/V tiles:
 //   head-pair mode (even GQA group): the SAME rows of two q heads of one kv head (128-row items);
 //   row-pair mode  (odd group, e.g. 5): two consecutive row tiles of one q head (256-row items).
+//   packed head-pair mode (group divisible by 4, a query tile with <= 64 rows inside its sequence -- the tail tile of
+//   a chunk, a 64-token branch of a shared prefix): every 128-row tile holds 64 rows of TWO q heads (rows 0..63 head h,
+//   rows 64..127 head h+1), so the unit covers four q heads and no MMA row is wasted on padding; the units of the
+//   item's upper half (sub >= Hq/4) are empty.
 struct Unit {
-    int b, q0, Lq, k0, Lk, kvh, head0, head1, r0, r1, n_t0, n_t1, n_max;
+    int b, q0, Lq, k0, Lk, kvh, head0, head1, r0, r1, n_t0, n_t1, n_max, pack;
     __device__ __forceinline__ int nt(int t) const { return t == 0 ? n_t0 : n_t1; }
     __device__ __forceinline__ int head(int t) const { return t == 0 ? head0 : head1; }
     __device__ __forceinline__ int rbegin(int t) const { return t == 0 ? r0 : r1; }
@@ -96,19 +104,28 @@ __device__ __forceinline__ void decode_unit(const PersistParams& p, int w, const
     u.b = r.a.x;
     const int mt = r.a.y;
     u.q0 = r.a.z; u.Lq = r.a.w; u.k0 = r.b.x; u.Lk = r.b.y;
+    u.pack = 1;
+    bool empty = false;
     if (p.pair_heads) {
-        u.head0 = 2 * sub; u.head1 = 2 * sub + 1;
         u.r0 = u.r1 = mt * TC_BM;
+        if (PS_PACK && p.pack_ok && u.Lq - u.r0 <= TC_BM / 2) {
+            u.pack = 2;
+            empty = 4 * sub >= p.Hq;
+            u.head0 = 4 * sub; u.head1 = 4 * sub + 2;
+        } else {
+            u.head0 = 2 * sub; u.head1 = 2 * sub + 1;
+        }
     } else {
         u.head0 = u.head1 = sub;
         u.r0 = mt * 2 * TC_BM; u.r1 = u.r0 + TC_BM;
     }
     u.kvh = (int)(((uint32_t)u.head0 * p.g_magic16) >> 16);       // head0 / G, exact for head0, G <= 128
     const int offset = u.Lk - u.Lq;
-    int kv_end0 = min(u.Lk, u.r0 + TC_BM + offset);
-    if (u.r0 >= u.Lq || kv_end0 < 0) kv_end0 = 0;
-    int kv_end1 = min(u.Lk, u.r1 + TC_BM + offset);
-    if (u.r1 >= u.Lq || kv_end1 < 0) kv_end1 = 0;
+    const int rows = TC_BM / u.pack;                        // query rows per head in a tile
+    int kv_end0 = min(u.Lk, u.r0 + rows + offset);
+    if (u.r0 >= u.Lq || kv_end0 < 0 || empty) kv_end0 = 0;
+    int kv_end1 = min(u.Lk, u.r1 + rows + offset);
+    if (u.r1 >= u.Lq || kv_end1 < 0 || empty) kv_end1 = 0;
     u.n_t0 = (kv_end0 + TC_BN - 1) / TC_BN;
     u.n_t1 = (kv_end1 + TC_BN - 1) / TC_BN;
     u.n_max = max(u.n_t0, u.n_t1);
@@ -239,7 +256,7 @@ constexpr int ps_threads(int wgs) { return wgs == 2 ? 640 : 384; }
 template <int EMU, bool TRACE = false, int WGS = 1>
 __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
     const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
-    const __grid_constant__ CUtensorMap map_v, const PersistParams p) {
+    const __grid_constant__ CUtensorMap map_v, const __grid_constant__ CUtensorMap map_q64, const PersistParams p) {
     using L = PsSmem;
     constexpr int S = TC_KV_STAGES;
     extern __shared__ uint8_t smem_raw[];
@@ -286,6 +303,7 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_q) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_q64) : "memory");
     }
     tc_fence_before();
     __syncthreads();
@@ -304,6 +322,21 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
                 auto pstamp = [&](int e) {
                     if (TRACE && blockIdx.x == 0 && tiles0 < p.trace_tiles) p.trace[(3 * p.trace_tiles + tiles0) * 8 + e] = clock64();
                 };
+                // Q tile t: 128 rows of one head, or (packed) 64 rows of head and of head + 1 stacked -- two 64-row boxes
+                // per 64-dim half; 64 rows x 128 B = 8 swizzle atoms, so the second box keeps the first one's phase
+                auto load_q = [&](int t, int head, int row, int pack) {
+                    const uint32_t dst = sQ + t * TC_TILE_BYTES;
+                    if (pack == 1) {
+                        tma_load_3d(dst, &map_q, q_full(t), 0, head, row);
+                        tma_load_3d(dst + TC_HALF_BYTES, &map_q, q_full(t), 64, head, row);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 2; ++i) {
+                            tma_load_3d(dst + i * (TC_HALF_BYTES / 2), &map_q64, q_full(t), 0, head + i, row);
+                            tma_load_3d(dst + TC_HALF_BYTES + i * (TC_HALF_BYTES / 2), &map_q64, q_full(t), 64, head + i, row);
+                        }
+                    }
+                };
                 Unit u;
                 UnitWalk walk;
                 walk.begin(p);
@@ -315,15 +348,13 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
                         pstamp(4);                               // Q slot 0 free -> Q load issued
                         ++q_use0;
                         mbar_expect_tx(q_full(0), TC_TILE_BYTES);
-                        tma_load_3d(sQ, &map_q, q_full(0), 0, u.head0, u.q0 + u.r0);
-                        tma_load_3d(sQ + TC_HALF_BYTES, &map_q, q_full(0), 64, u.head0, u.q0 + u.r0);
+                        load_q(0, u.head0, u.q0 + u.r0, u.pack);
                     }
                     if (u.n_t1 > 0) {
                         mbar_wait(q_empty(1), (q_use1 & 1u) ^ 1u);
                         ++q_use1;
                         mbar_expect_tx(q_full(1), TC_TILE_BYTES);
-                        tma_load_3d(sQ + TC_TILE_BYTES, &map_q, q_full(1), 0, u.head1, u.q0 + u.r1);
-                        tma_load_3d(sQ + TC_TILE_BYTES + TC_HALF_BYTES, &map_q, q_full(1), 64, u.head1, u.q0 + u.r1);
+                        load_q(1, u.head1, u.q0 + u.r1, u.pack);
                     }
                     const int32_t* bt = paged ? p.block_tables + (int64_t)u.b * p.bt_row_stride : nullptr;
                     for (int j = 0; j < u.n_max; ++j, ++kv_it) {
@@ -653,7 +684,8 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
                 p.trace[((4 + t) * p.trace_tiles + (s_cnt - 1)) * 8 + 7] = clock64();
             const int nt = u.nt(t);
             const int r_begin = u.rbegin(t);
-            const int row = r_begin + row_in_tile;                  // query index within the sequence
+            // packed tiles: rows 0..63 belong to head(t), rows 64..127 to head(t) + 1, both at query rows r_begin + 0..63
+            const int row = r_begin + (u.pack == 2 ? (row_in_tile & 63) : row_in_tile);   // query index within the sequence
             const int offset = u.Lk - u.Lq;
             float m_used = -INFINITY;                               // running maximum, scaled (log2) domain
             uint64_t l2 = pack2(0.f, 0.f);                          // two partial row sums
@@ -799,7 +831,8 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
                 const uint64_t inv2 = pack2(inv, inv);
                 uint8_t* stage = smem_gen + L::STAGE_OFF + t * L::STAGE_BYTES;
                 const int tid_wg = (warp & 3) * 32 + lane;          // == row_in_tile
-                const int rows_valid = min(TC_BM, u.Lq - r_begin);  // rows of this tile inside the sequence
+                const int rmask = u.pack == 2 ? 63 : 127, rshift = u.pack == 2 ? 6 : 7;   // tile row -> (head, query row)
+                const int rows_valid = min(rmask + 1, u.Lq - r_begin);   // query rows of this tile inside the sequence
                 __nv_bfloat16* obase = p.out + (int64_t)(u.q0 + r_begin) * p.out_token_stride + (int64_t)u.head(t) * B200_HD;
 #pragma unroll
                 for (int pass = 0; pass < 2; ++pass) {
@@ -826,9 +859,10 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
 #pragma unroll
                     for (int step = 0; step < 8; ++step) {
                         const int r = step * 16 + (tid_wg >> 3), chunk = tid_wg & 7;
-                        if (r < rows_valid) {
+                        const int qi = r & rmask, hi = r >> rshift;
+                        if (qi < rows_valid) {
                             const int4 v = *reinterpret_cast<const int4*>(stage + r * 128 + ((chunk ^ (r & 7)) << 4));
-                            *reinterpret_cast<int4*>(obase + (int64_t)r * p.out_token_stride + pass * 64 + chunk * 8) = v;
+                            *reinterpret_cast<int4*>(obase + (int64_t)qi * p.out_token_stride + hi * B200_HD + pass * 64 + chunk * 8) = v;
                         }
                     }
                     estamp(3 + 2 * pass);
@@ -853,14 +887,14 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
     }
 }
 
-const CUtensorMap* cached_map(const void* base, uint64_t rows, uint64_t heads, uint64_t row_stride_elems) {
+const CUtensorMap* cached_map(const void* base, uint64_t rows, uint64_t heads, uint64_t row_stride_elems, uint32_t box_rows) {
     static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
-    const MapKey key{base, rows, heads, row_stride_elems, current_device()};
+    const MapKey key{base, rows, heads, row_stride_elems | ((uint64_t)box_rows << 48), current_device()};
     auto it = cache.find(key);
     if (it != cache.end()) return &it->second;
     if (cache.size() >= 4096) cache.clear();                  // bounded; K/V cache maps are re-encoded on demand
     CUtensorMap m;
-    if (!make_map(&m, base, rows, heads, row_stride_elems)) return nullptr;
+    if (!make_map(&m, base, rows, heads, row_stride_elems, box_rows)) return nullptr;
     return &cache.emplace(key, m).first->second;
 }
 
@@ -870,7 +904,7 @@ static int g_trace_tiles = 0;
 int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32_t max_items, cudaStream_t stream) {
     if (a.batch == 0 || a.total_q == 0 || a.max_q == 0) return 0;
     if (get_encode_fn() == nullptr) return -6;
-    using KernelFn = void (*)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const PersistParams);
+    using KernelFn = void (*)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap, const PersistParams);
     static const KernelFn kernels[2][5] = {
         {prefill_persist_kernel<0, false, 1>, prefill_persist_kernel<1, false, 1>, prefill_persist_kernel<2, false, 1>,
          prefill_persist_kernel<3, false, 1>, prefill_persist_kernel<4, false, 1>},
@@ -895,6 +929,7 @@ int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32
     }
     const bool paged = a.block_tables != nullptr;
     const CUtensorMap* pq = cached_map(a.q, (uint64_t)a.total_q, (uint64_t)a.Hq, (uint64_t)a.q_token_stride);
+    const CUtensorMap* pq64 = cached_map(a.q, (uint64_t)a.total_q, (uint64_t)a.Hq, (uint64_t)a.q_token_stride, 64);
     const CUtensorMap *pk, *pv;
     if (paged) {
         const uint64_t rows = (uint64_t)a.num_cache_blocks * B200_PAGE;
@@ -904,8 +939,8 @@ int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32
         pk = cached_map(a.k, (uint64_t)a.total_q, (uint64_t)a.Hkv, (uint64_t)a.k_token_stride);
         pv = cached_map(a.v, (uint64_t)a.total_q, (uint64_t)a.Hkv, (uint64_t)a.v_token_stride);
     }
-    if (!pq || !pk || !pv) return -6;
-    const CUtensorMap &mq = *pq, &mk = *pk, &mv = *pv;
+    if (!pq || !pk || !pv || !pq64) return -6;
+    const CUtensorMap &mq = *pq, &mk = *pk, &mv = *pv, &mq64 = *pq64;
     PersistParams p;
     p.cu_q = a.cu_q; p.cu_k = a.cu_k; p.block_tables = a.block_tables; p.bt_row_stride = a.bt_row_stride;
     p.out = (__nv_bfloat16*)a.out; p.out_token_stride = a.out_token_stride;
@@ -914,6 +949,7 @@ int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32
     p.per_item = (uint32_t)(p.pair_heads ? a.Hq / 2 : a.Hq);
     p.per_item_magic = p.per_item <= 1 ? 0u : (uint32_t)((0x100000000ull + p.per_item - 1) / p.per_item);
     p.g_magic16 = (uint32_t)((65536 + p.G - 1) / p.G);
+    p.pack_ok = (p.pair_heads && p.G % 4 == 0 && wgs == 1 && !getenv("B200ATTN_PREFILL_NOPACK")) ? 1 : 0;
     p.plan = plan; p.items = plan + plan_items_offset(a.batch);
     int64_t units = (int64_t)max_items * (p.pair_heads ? a.Hq / 2 : a.Hq);
     int grid = sm_count();
@@ -927,10 +963,10 @@ int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32
             cudaFuncSetAttribute(prefill_persist_kernel<PREFILL_EMU_DEFAULT, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, PsSmem::ALLOC);
             trace_once.done();
         }
-        if (wgs == 2) prefill_persist_kernel<PREFILL_EMU_DEFAULT, true, 2><<<grid, ps_threads(2), PsSmem::ALLOC, stream>>>(mq, mk, mv, p);
-        else prefill_persist_kernel<PREFILL_EMU_DEFAULT, true, 1><<<grid, ps_threads(1), PsSmem::ALLOC, stream>>>(mq, mk, mv, p);
+        if (wgs == 2) prefill_persist_kernel<PREFILL_EMU_DEFAULT, true, 2><<<grid, ps_threads(2), PsSmem::ALLOC, stream>>>(mq, mk, mv, mq64, p);
+        else prefill_persist_kernel<PREFILL_EMU_DEFAULT, true, 1><<<grid, ps_threads(1), PsSmem::ALLOC, stream>>>(mq, mk, mv, mq64, p);
     } else {
-        kernels[wgs - 1][emu]<<<grid, ps_threads(wgs), PsSmem::ALLOC, stream>>>(mq, mk, mv, p);
+        kernels[wgs - 1][emu]<<<grid, ps_threads(wgs), PsSmem::ALLOC, stream>>>(mq, mk, mv, mq64, p);
     }
     return (int)cudaGetLastError();
 }

@@ -179,10 +179,11 @@ static inline EncodeTiledFn get_encode_fn() {
 }
 
 // 3-D map over [rows][heads][128] bf16 with a row stride; box = 128 rows x 1 head x 64 dims.
-static inline bool make_map(CUtensorMap* m, const void* base, uint64_t rows, uint64_t heads, uint64_t row_stride_elems) {
+static inline bool make_map(CUtensorMap* m, const void* base, uint64_t rows, uint64_t heads, uint64_t row_stride_elems,
+                            uint32_t box_rows = 128) {
     const cuuint64_t dims[3] = {128, heads, rows};
     const cuuint64_t strides[2] = {128 * 2, row_stride_elems * 2};
-    const cuuint32_t box[3] = {64, 1, 128};
+    const cuuint32_t box[3] = {64, 1, box_rows};
     const cuuint32_t estr[3] = {1, 1, 1};
     return get_encode_fn()(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -208,6 +209,7 @@ struct MapKeyHash {
         return (size_t)(h ^ (h >> 29));
     }
 };
-const CUtensorMap* cached_map(const void* base, uint64_t rows, uint64_t heads, uint64_t row_stride_elems);   // attn_prefill_persist.cu
+const CUtensorMap* cached_map(const void* base, uint64_t rows, uint64_t heads, uint64_t row_stride_elems,
+                              uint32_t box_rows = 128);   // attn_prefill_persist.cu
 
 }  // namespace b200
