@@ -180,9 +180,10 @@ class StepPlan:
         self.buf, self.batch, self.total_q, self.route_decode, self.heads = buf, batch, total_q, route_decode, heads
 
     def counts(self):
-        """(prefill work items, decode rows) -- synchronises; for tests and tools only."""
-        head = self.buf[:8].view(torch.int32).cpu()
-        return int(head[0]), int(head[1])
+        """(prefill work items = query tiles of multi-token rows, decode rows) -- synchronises; for tests and tools only.
+        plan words: [0] work units, [1] decode rows, [2] tile rows, [3] items."""
+        head = self.buf[:16].view(torch.int32).cpu()
+        return int(head[3]), int(head[1])
 
 
 def attn_plan(cu_seqlens_q: torch.Tensor, cu_seqlens_k: torch.Tensor, total_q: int, num_heads: int, num_kv_heads: int,

@@ -205,8 +205,10 @@ int b200_attn_plan(const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k, int
     if (!cu_seqlens_q || !cu_seqlens_k || !plan) return B200_ERR_NULL;
     if (!aligned16(plan)) return B200_ERR_ALIGN;
     if (plan_bytes_given < plan_bytes(batch > 0 ? batch : 1, total_q)) return B200_ERR_WORKSPACE;
+    if (plan_units_per_item(num_heads, num_kv_heads) > PLAN_MAX_UNITS_PER_ITEM) return B200_ERR_SHAPE;
     return launch_attn_plan(cu_seqlens_q, cu_seqlens_k, batch, route_decode ? 1 : 0,
-                            plan_tile_rows(num_heads, num_kv_heads), (int32_t*)plan,
+                            plan_tile_rows(num_heads, num_kv_heads), plan_units_per_item(num_heads, num_kv_heads),
+                            prefill_pack_ok(num_heads, num_kv_heads) ? 1 : 0, (int32_t*)plan,
                             plan_max_items(batch, total_q), (cudaStream_t)stream);
 }
 

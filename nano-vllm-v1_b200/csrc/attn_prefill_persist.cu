@@ -26,8 +26,7 @@ struct PersistParams {
     const int32_t* cu_q; const int32_t* cu_k; const int32_t* block_tables; int32_t bt_row_stride;
     __nv_bfloat16* out; int64_t out_token_stride;
     int32_t Hq, G, pair_heads; float scale_log2;
-    int32_t pack_ok;                               // short query tiles may pack two q heads per 128-row tile (see Unit::pack)
-    uint32_t per_item, per_item_magic, g_magic16;   // units per item; ceil(2^32 / per_item); ceil(2^16 / G): exact division by multiply-high
+    uint32_t g_magic16;                            // ceil(2^16 / G): head / G by multiply-high
     const int32_t* plan; const int32_t* items;
     long long* trace; int32_t trace_tiles;      // TRACE builds only: clock64 stamps of CTA 0 (b200_debug_prefill_trace)
 };
@@ -80,41 +79,28 @@ __device__ __forceinline__ int snake(int k, int c, int g) { return (k & 1) ? (k 
 // load level (two 16-byte loads of the plan's item record) one unit AHEAD: on this part an L2 hit costs
 // ~800 cycles, and three dependent levels (count -> item -> cu_seqlens) in front of every unit left the tensor
 // pipe idle for ~3,000 cycles per unit while the MMA issuer found out what to do next.
-struct RawUnit { int4 a; int4 b; };          // {sequence, tile, q0, Lq} {k0, Lk, -, -}
-__device__ __forceinline__ int units_per_item(const PersistParams& p) { return (int)p.per_item; }
-// floor(w / per_item) without a division sequence (~100 cycles of dependent MUFU/convert work each, four of them per
-// unit boundary in every role): exact while w * per_item < 2^32, i.e. for any launch the plan can describe.
-__device__ __forceinline__ int item_of(const PersistParams& p, int w) {
-    return p.per_item == 1 ? w : (int)__umulhi((uint32_t)w, p.per_item_magic);
-}
+struct RawUnit { int4 a; int4 b; };          // {sequence, tile, q0, Lq} {k0, Lk, sub, pack}: one record of the plan's unit table
 __device__ __forceinline__ RawUnit fetch_unit(const PersistParams& p, int w, int n_units) {
     RawUnit r;
     r.a = make_int4(0, 0, 0, 0); r.b = r.a;
     if (w < n_units) {
         // volatile asm: an ordinary read-only load is free to be sunk to its first use (the next unit's start),
         // which is exactly the latency this fetch-ahead exists to hide
-        const int4* rec = reinterpret_cast<const int4*>(p.items) + 2 * item_of(p, w);
+        const int4* rec = reinterpret_cast<const int4*>(p.items) + 2 * w;
         asm volatile("ld.global.nc.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(r.a.x), "=r"(r.a.y), "=r"(r.a.z), "=r"(r.a.w) : "l"(rec));
-        asm volatile("ld.global.nc.v2.s32 {%0,%1}, [%2];" : "=r"(r.b.x), "=r"(r.b.y) : "l"(rec + 1));
+        asm volatile("ld.global.nc.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(r.b.x), "=r"(r.b.y), "=r"(r.b.z), "=r"(r.b.w) : "l"(rec + 1));
     }
     return r;
 }
-__device__ __forceinline__ void decode_unit(const PersistParams& p, int w, const RawUnit& r, Unit& u) {
-    const int sub = w - item_of(p, w) * units_per_item(p);
+__device__ __forceinline__ void decode_unit(const PersistParams& p, const RawUnit& r, Unit& u) {
     u.b = r.a.x;
-    const int mt = r.a.y;
+    const int mt = r.a.y, sub = r.b.z;
     u.q0 = r.a.z; u.Lq = r.a.w; u.k0 = r.b.x; u.Lk = r.b.y;
-    u.pack = 1;
-    bool empty = false;
+    u.pack = r.b.w;
     if (p.pair_heads) {
         u.r0 = u.r1 = mt * TC_BM;
-        if (PS_PACK && p.pack_ok && u.Lq - u.r0 <= TC_BM / 2) {
-            u.pack = 2;
-            empty = 4 * sub >= p.Hq;
-            u.head0 = 4 * sub; u.head1 = 4 * sub + 2;
-        } else {
-            u.head0 = 2 * sub; u.head1 = 2 * sub + 1;
-        }
+        if (u.pack == 2) { u.head0 = 4 * sub; u.head1 = 4 * sub + 2; }
+        else { u.head0 = 2 * sub; u.head1 = 2 * sub + 1; }
     } else {
         u.head0 = u.head1 = sub;
         u.r0 = mt * 2 * TC_BM; u.r1 = u.r0 + TC_BM;
@@ -123,9 +109,9 @@ __device__ __forceinline__ void decode_unit(const PersistParams& p, int w, const
     const int offset = u.Lk - u.Lq;
     const int rows = TC_BM / u.pack;                        // query rows per head in a tile
     int kv_end0 = min(u.Lk, u.r0 + rows + offset);
-    if (u.r0 >= u.Lq || kv_end0 < 0 || empty) kv_end0 = 0;
+    if (u.r0 >= u.Lq || kv_end0 < 0) kv_end0 = 0;
     int kv_end1 = min(u.Lk, u.r1 + rows + offset);
-    if (u.r1 >= u.Lq || kv_end1 < 0 || empty) kv_end1 = 0;
+    if (u.r1 >= u.Lq || kv_end1 < 0) kv_end1 = 0;
     u.n_t0 = (kv_end0 + TC_BN - 1) / TC_BN;
     u.n_t1 = (kv_end1 + TC_BN - 1) / TC_BN;
     u.n_max = max(u.n_t0, u.n_t1);
@@ -136,7 +122,7 @@ __device__ __forceinline__ void decode_unit(const PersistParams& p, int w, const
 struct UnitWalk {
     int n_units, k; RawUnit raw;
     __device__ __forceinline__ void begin(const PersistParams& p) {
-        n_units = __ldg(p.plan) * units_per_item(p);
+        n_units = __ldg(p.plan);
         k = 0;
         raw = fetch_unit(p, snake(0, (int)blockIdx.x, (int)gridDim.x), n_units);
     }
@@ -144,7 +130,7 @@ struct UnitWalk {
     __device__ __forceinline__ bool next(const PersistParams& p, Unit& u) {
         const int w = snake(k, (int)blockIdx.x, (int)gridDim.x);
         if (w >= n_units) return false;
-        decode_unit(p, w, raw, u);
+        decode_unit(p, raw, u);
         ++k;
         raw = fetch_unit(p, snake(k, (int)blockIdx.x, (int)gridDim.x), n_units);
         return true;
@@ -901,6 +887,26 @@ const CUtensorMap* cached_map(const void* base, uint64_t rows, uint64_t heads, u
 static long long* g_trace = nullptr;
 static int g_trace_tiles = 0;
 
+// softmax warpgroups per query tile (1 or 2): B200ATTN_PREFILL_WGS, read once
+static int prefill_wgs() {
+    static int wgs = -1;
+    if (wgs < 0) {
+        const char* env = getenv("B200ATTN_PREFILL_WGS");
+        wgs = (env ? atoi(env) : PREFILL_WGS_DEFAULT) == 2 ? 2 : 1;
+    }
+    return wgs;
+}
+
+// Decided where the step plan is built (b200_attn_plan): query tiles with <= 64 rows inside their sequence carry two q
+// heads per 128-row tile when the unit's four heads share one kv head (group divisible by 4) and the kernel variant
+// maps rows to (head, query) pairs (WGS = 1).  B200ATTN_PREFILL_NOPACK=1 turns it off (A/B).
+bool prefill_pack_ok(int32_t Hq, int32_t Hkv) {
+    static int nopack = -1;
+    if (nopack < 0) nopack = getenv("B200ATTN_PREFILL_NOPACK") ? 1 : 0;
+    const int G = Hq / Hkv;
+    return PS_PACK && !nopack && prefill_wgs() == 1 && G % 4 == 0;
+}
+
 int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32_t max_items, cudaStream_t stream) {
     if (a.batch == 0 || a.total_q == 0 || a.max_q == 0) return 0;
     if (get_encode_fn() == nullptr) return -6;
@@ -910,7 +916,8 @@ int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32
          prefill_persist_kernel<3, false, 1>, prefill_persist_kernel<4, false, 1>},
         {prefill_persist_kernel<0, false, 2>, prefill_persist_kernel<1, false, 2>, prefill_persist_kernel<2, false, 2>,
          prefill_persist_kernel<3, false, 2>, prefill_persist_kernel<4, false, 2>}};
-    static int emu = -1, wgs = -1;
+    static int emu = -1;
+    const int wgs = prefill_wgs();
     static PerDeviceOnce once;                                   // the shared-memory opt-in is per device
     if (once.need()) {
         for (int w = 0; w < 2; ++w)
@@ -924,8 +931,6 @@ int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32
         const char* env = getenv("B200ATTN_PREFILL_EMU");        // A/B knob; default chosen by measurement
         int v = env ? atoi(env) : PREFILL_EMU_DEFAULT;
         emu = v < 0 ? 0 : (v > 4 ? 4 : v);
-        env = getenv("B200ATTN_PREFILL_WGS");                    // softmax warpgroups per query tile (1 or 2)
-        wgs = (env ? atoi(env) : PREFILL_WGS_DEFAULT) == 2 ? 2 : 1;
     }
     const bool paged = a.block_tables != nullptr;
     const CUtensorMap* pq = cached_map(a.q, (uint64_t)a.total_q, (uint64_t)a.Hq, (uint64_t)a.q_token_stride);
@@ -946,11 +951,8 @@ int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32
     p.out = (__nv_bfloat16*)a.out; p.out_token_stride = a.out_token_stride;
     p.Hq = a.Hq; p.G = a.Hq / a.Hkv; p.scale_log2 = a.scale * 1.4426950408889634f;
     p.pair_heads = plan_tile_rows(a.Hq, a.Hkv) == 128 ? 1 : 0;
-    p.per_item = (uint32_t)(p.pair_heads ? a.Hq / 2 : a.Hq);
-    p.per_item_magic = p.per_item <= 1 ? 0u : (uint32_t)((0x100000000ull + p.per_item - 1) / p.per_item);
     p.g_magic16 = (uint32_t)((65536 + p.G - 1) / p.G);
-    p.pack_ok = (p.pair_heads && p.G % 4 == 0 && wgs == 1 && !getenv("B200ATTN_PREFILL_NOPACK")) ? 1 : 0;
-    p.plan = plan; p.items = plan + plan_items_offset(a.batch);
+    p.plan = plan; p.items = plan + plan_units_offset(a.batch, max_items);      // the unit table (launch.h)
     int64_t units = (int64_t)max_items * (p.pair_heads ? a.Hq / 2 : a.Hq);
     int grid = sm_count();
     if (units < grid) grid = (int)units;

@@ -70,24 +70,32 @@ int launch_attn_prefill_tc1(const PrefillArgs& a, cudaStream_t stream);  // same
 bool prefill_tc_available();
 
 // ---- step plan (attn_plan.cu) + persistent tcgen05 prefill (attn_prefill_persist.cu) ----------
-// plan buffer, int32 words: [0] n_items  [1] n_decode_rows  [2] tile_rows  [3..15] reserved
+// plan buffer, int32 words: [0] n_units  [1] n_decode_rows  [2] tile_rows  [3] n_items  [4..15] reserved
 //                           [16 .. 16 + batch)        rows with exactly one query token (region padded to 4 words)
-//                           [.. + 8*max_items)        one 32-byte record per (sequence, query tile) work item, heaviest
-//                                                     first: {sequence, tile, q0, Lq, k0, Lk, 0, 0} -- everything the
-//                                                     prefill kernel needs about an item in ONE load level, so it can
-//                                                     fetch the next unit's record while the current unit runs
+//                           [.. + 4*max_items)        scratch of the plan kernel: {sequence, tile, first unit, units} per item
+//                           [.. + 8*max_units)        one 32-byte record per WORK UNIT of the persistent prefill kernel,
+//                                                     heaviest first: {sequence, tile, q0, Lq} {k0, Lk, sub, pack} -- all a
+//                                                     role needs about its next unit in ONE load level.  An item (query tile
+//                                                     of a sequence) has Hq/2 units (two q heads each), Hq/4 when its tile is
+//                                                     packed (<= 64 valid rows, two heads per tile), Hq in row-pair mode.
 constexpr int PLAN_HEADER_WORDS = 16;
-constexpr int PLAN_ITEM_WORDS = 8;
-constexpr size_t plan_items_offset(int32_t batch) { return (size_t)PLAN_HEADER_WORDS + (((size_t)batch + 3) & ~(size_t)3); }
+constexpr int PLAN_ITEM_WORDS = 4;
+constexpr int PLAN_UNIT_WORDS = 8;
+constexpr int PLAN_MAX_UNITS_PER_ITEM = 64;      // Hq <= 128 in pair mode, <= 64 in row-pair mode
 constexpr int PLAN_TILE_ROWS_MIN = 128;
 // tile rows of a launch: 128 when two q heads of one kv head share a CTA (even GQA group), else 256
 inline int32_t plan_tile_rows(int32_t Hq, int32_t Hkv) { return ((Hq / Hkv) % 2 == 0) ? 128 : 256; }
+inline int32_t plan_units_per_item(int32_t Hq, int32_t Hkv) { return plan_tile_rows(Hq, Hkv) == 128 ? Hq / 2 : Hq; }
 inline int32_t plan_max_items(int32_t batch, int32_t total_q) { return total_q / PLAN_TILE_ROWS_MIN + batch; }
+constexpr size_t plan_items_offset(int32_t batch) { return (size_t)PLAN_HEADER_WORDS + (((size_t)batch + 3) & ~(size_t)3); }
+constexpr size_t plan_units_offset(int32_t batch, int32_t max_items) { return plan_items_offset(batch) + (size_t)PLAN_ITEM_WORDS * max_items; }
 inline size_t plan_bytes(int32_t batch, int32_t total_q) {
-    return (plan_items_offset(batch) + PLAN_ITEM_WORDS * (size_t)plan_max_items(batch, total_q)) * sizeof(int32_t);
+    const int32_t mi = plan_max_items(batch, total_q);
+    return (plan_units_offset(batch, mi) + (size_t)PLAN_UNIT_WORDS * PLAN_MAX_UNITS_PER_ITEM * mi) * sizeof(int32_t);
 }
+bool prefill_pack_ok(int32_t Hq, int32_t Hkv);     // attn_prefill_persist.cu: may short query tiles pack two heads per tile?
 int launch_attn_plan(const int32_t* cu_q, const int32_t* cu_k, int32_t batch, int32_t route_decode, int32_t tile_rows,
-                     int32_t* plan, int32_t max_items, cudaStream_t stream);
+                     int32_t units_per_item, int32_t pack_ok, int32_t* plan, int32_t max_items, cudaStream_t stream);
 int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32_t max_items, cudaStream_t stream);
 
 
