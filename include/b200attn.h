@@ -182,7 +182,7 @@ int b200_attn_prefill(const void* q, int64_t q_token_stride,
  * (2'/3') Planned varlen attention for mixed batches.  The reference hands
  *     flash_attn_varlen_func one call per layer whatever the mix of rows (attention.py:242-248);
  *     here a step plan built ON THE DEVICE from cu_seqlens routes
- *       rows with q_len > 1  -> persistent tcgen05 prefill kernel (work list sorted heaviest-first),
+ *       rows with q_len > 1  -> persistent tcgen05 prefill kernel (per-unit work table sorted heaviest-first),
  *       rows with q_len == 1 -> split-K decode kernel (only when a block table exists),
  *     and is reused by every layer of the step.  No host reads, graph-capturable.
  *     plan: b200_attn_plan_bytes(batch, total_q) bytes of device memory, 16-byte aligned; it is built for

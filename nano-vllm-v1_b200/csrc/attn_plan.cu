@@ -2,10 +2,13 @@
 //
 // One tiny kernel, run ONCE per engine step (every layer of the step reuses its output), turns
 // cu_seqlens_q/k into
-//   * a work list for the persistent tcgen05 prefill kernel: one item per query tile (128 rows when the
-//     kernel pairs two q heads of a GQA group per CTA, else 256 rows) of a sequence with q_len > 1 (or every sequence when routing is off), ordered by
-//     descending number of KV tiles (longest-processing-time-first for the static round-robin
-//     over the persistent CTAs);
+//   * the UNIT TABLE of the persistent tcgen05 prefill kernel: one 32-byte record per work unit (two query tiles
+//     sharing a K/V stream; launch.h), for every query tile (128 rows when the kernel pairs q heads of a GQA group,
+//     else 256 rows) of a sequence with q_len > 1 (or every sequence when routing is off), in descending order of
+//     KV tiles (longest-processing-time-first for the static snake over the persistent CTAs).  An item
+//     contributes Hq/2 units, Hq/4 when its tile is packed (<= 64 valid rows: two heads per tile), Hq in row-pair
+//     mode, so the counting sort runs on unit counts: weighted histogram -> scan -> every item claims its run of
+//     unit slots -> all threads expand items into unit records;
 //   * the list of rows with exactly one query token, which go to the split-K decode kernel
 //     (a 128-row UMMA tile would be <1 % utilised by such a row).
 // Everything stays on the device: no host read of lengths, so the call is graph-capturable.
