@@ -756,3 +756,42 @@ print("ok")
        os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "nano-vllm-v1_b200"))
     r = subprocess.run([sys.executable, "-c", code], env={**os.environ, **env}, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "ok" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+@pytest.mark.parametrize("Hq,Hkv", [(8, 1), (32, 8), (16, 8), (20, 4)])
+def test_step_plan_unit_table_is_complete_and_heaviest_first(ops, Hq, Hkv):
+    """The plan's per-unit table (csrc/launch.h): every (sequence, query tile, sub-unit) exactly once, packed tiles
+    (<= 64 valid rows, group divisible by 4) with half the units and the pack flag, records carrying q0/Lq/k0/Lk, and the
+    whole list in non-increasing order of K/V tiles (what the static snake over the CTAs relies on)."""
+    lens_q = [64, 300, 1, 128, 40, 1, 513, 65, 2]
+    lens_k = [700, 300, 900, 128, 1000, 5, 513, 65, 258]
+    B, T = len(lens_q), sum(lens_q)
+    cu_q = torch.tensor([0] + torch.tensor(lens_q).cumsum(0).tolist(), dtype=torch.int32, device="cuda")
+    cu_k = torch.tensor([0] + torch.tensor(lens_k).cumsum(0).tolist(), dtype=torch.int32, device="cuda")
+    plan = ops.attn_plan(cu_q, cu_k, T, Hq, Hkv, route_decode=True)
+    w = plan.buf.view(torch.int32).cpu()
+    G = Hq // Hkv
+    tile = 128 if G % 2 == 0 else 256
+    per_item = Hq // 2 if tile == 128 else Hq
+    pack_ok = tile == 128 and G % 4 == 0
+    max_items = T // 128 + B
+    off = 16 + ((B + 3) & ~3) + 4 * max_items
+    n_units, n_dec, tile_rows, n_items = (int(x) for x in w[:4])
+    assert tile_rows == tile and n_dec == sum(1 for x in lens_q if x == 1)
+    want = {}
+    for b, (lq, lk) in enumerate(zip(lens_q, lens_k)):
+        if lq <= 1:
+            continue
+        for mt in range((lq + tile - 1) // tile):
+            packed = pack_ok and lq - mt * 128 <= 64
+            for sub in range(per_item // 2 if packed else per_item):
+                want[(b, mt, sub)] = 2 if packed else 1
+    assert n_items == len({(b, mt) for b, mt, _ in want}) and n_units == len(want)
+    recs = w[off:off + 8 * n_units].view(n_units, 8).tolist()
+    seen, keys = {}, []
+    for b, mt, q0, lq, k0, lk, sub, pack in recs:
+        assert (q0, lq, k0, lk) == (int(cu_q[b]), lens_q[b], int(cu_k[b]), lens_k[b])
+        seen[(b, mt, sub)] = pack
+        keys.append((min(lk, (mt + 1) * tile + lk - lq) + 127) // 128)
+    assert seen == want
+    assert all(a >= b for a, b in zip(keys, keys[1:])), keys
