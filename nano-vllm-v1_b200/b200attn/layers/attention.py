@@ -77,7 +77,7 @@ class Attention(nn.Module):
         plan = getattr(context, "_b200_plan", None)
         if plan is None or plan.total_q != q.shape[0]:
             plan = ops.attn_plan(context.cu_seqlens_q, context.cu_seqlens_k, q.shape[0], self.num_heads,
-                                 self.num_kv_heads, route_decode=context.block_tables is not None)
+                                 self.num_kv_heads, route_decode=context.block_tables is not None, reuse=True)
             try:
                 context._b200_plan = plan                     # every layer of this step reuses it
             except AttributeError:

@@ -186,14 +186,33 @@ class StepPlan:
         return int(head[3]), int(head[1])
 
 
+_PLAN_RING = {}          # device index -> [buffers, next slot]: the engine's per-step plans alternate between two buffers
+
+
+def _plan_buffer(nbytes: int, device: torch.device) -> torch.Tensor:
+    """A plan buffer that lives until the plan after next is built (the engine builds one plan per step, uses it for
+    that step's layers only, and everything is ordered on one stream): no allocation on the step path once the largest
+    step has been seen (the ABI side never allocates; this keeps the host side from doing it per step)."""
+    ring = _PLAN_RING.setdefault(device.index, [[None, None], 0])
+    slot = ring[1]
+    ring[1] = slot ^ 1
+    buf = ring[0][slot]
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        ring[0][slot] = buf
+    return buf[:nbytes]
+
+
 def attn_plan(cu_seqlens_q: torch.Tensor, cu_seqlens_k: torch.Tensor, total_q: int, num_heads: int, num_kv_heads: int,
-              route_decode: bool) -> StepPlan:
+              route_decode: bool, reuse: bool = False) -> StepPlan:
+    """reuse=True: the buffer comes from a two-deep ring (valid until the plan after next is built) -- what the
+    Attention layer asks for; the default allocates, so a caller may keep any number of plans alive."""
     _need_i32(cu_seqlens_q, "cu_seqlens_q")
     _need_i32(cu_seqlens_k, "cu_seqlens_k")
     B = cu_seqlens_q.numel() - 1
     lib = load_library()
     nbytes = lib.b200_attn_plan_bytes(max(B, 1), total_q)
-    buf = torch.empty(nbytes, dtype=torch.uint8, device=cu_seqlens_q.device)
+    buf = _plan_buffer(nbytes, cu_seqlens_q.device) if reuse else torch.empty(nbytes, dtype=torch.uint8, device=cu_seqlens_q.device)
     check(lib.b200_attn_plan(cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr(), B, total_q, num_heads, num_kv_heads,
                              1 if route_decode else 0, buf.data_ptr(), nbytes, _stream()), "b200_attn_plan")
     return StepPlan(buf, B, total_q, route_decode, (num_heads, num_kv_heads))
