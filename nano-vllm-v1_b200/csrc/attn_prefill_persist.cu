@@ -875,7 +875,7 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
 
 const CUtensorMap* cached_map(const void* base, uint64_t rows, uint64_t heads, uint64_t row_stride_elems, uint32_t box_rows) {
     static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
-    const MapKey key{base, rows, heads, row_stride_elems | ((uint64_t)box_rows << 48), current_device()};
+    const MapKey key{base, rows, heads, row_stride_elems, box_rows, current_device()};
     auto it = cache.find(key);
     if (it != cache.end()) return &it->second;
     if (cache.size() >= 4096) cache.clear();                  // bounded; K/V cache maps are re-encoded on demand

@@ -196,16 +196,16 @@ static inline bool make_map(CUtensorMap* m, const void* base, uint64_t rows, uin
 // costs three hash lookups instead of three cuTensorMapEncodeTiled driver calls.  Per process, one Python
 // thread per GPU process (the reference's model), bounded size.
 struct MapKey {
-    const void* base; uint64_t rows, heads, stride; int dev;
+    const void* base; uint64_t rows, heads, stride; uint32_t box_rows; int dev;
     bool operator==(const MapKey& o) const {
-        return base == o.base && rows == o.rows && heads == o.heads && stride == o.stride && dev == o.dev;
+        return base == o.base && rows == o.rows && heads == o.heads && stride == o.stride && box_rows == o.box_rows && dev == o.dev;
     }
 };
 struct MapKeyHash {
     size_t operator()(const MapKey& k) const {
         uint64_t h = (uint64_t)(uintptr_t)k.base * 0x9E3779B97F4A7C15ull;
         h ^= (k.rows + 0x632BE59BD9B4E019ull) * 0xC2B2AE3D27D4EB4Full;
-        h ^= (k.heads << 40) ^ (k.stride << 8) ^ (uint64_t)k.dev;
+        h ^= (k.heads << 40) ^ (k.stride << 8) ^ ((uint64_t)k.box_rows << 52) ^ (uint64_t)k.dev;
         return (size_t)(h ^ (h >> 29));
     }
 };
