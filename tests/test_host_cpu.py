@@ -225,3 +225,25 @@ def test_allreduce_form_policy_and_no_cpu_fallback():
     assert ops.ar_choose_form(2, 8 * MB, 4 * MB, 16 * MB) == 0            # a 2-rank message too big to push: pull
     with pytest.raises(RuntimeError):
         ops.tp_all_reduce_(torch.zeros(8, dtype=torch.bfloat16))
+
+
+def test_bench_reference_arm_prints_the_contract_line():
+    """`bench.py --impl reference` (the CPU oracle port timed on host cores; the one place besides tests/ and smoke()
+    that may execute oracle/) prints ONE JSON line with the keys the driver reads, and loads no native library."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "1"],
+                       capture_output=True, text=True, timeout=600, cwd=root)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "paged_attn_decode_hbm_gbps" and d["unit"] == "GB/s"
+    assert d["higher_is_better"] is True and d["n_gpus"] == 1 and d["steps"] == 1 and d["value"] > 0
+    assert d["config"]["workload"].startswith("qwen3-8b-decode-paged-attn-b512-ctx4096")
+    cb = d["cpu_baseline"]
+    assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and "sample" in cb
+    assert d["e2e"] == {"value": d["value"], "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert d["gpu_launches"] == 0
