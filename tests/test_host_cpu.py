@@ -247,3 +247,35 @@ def test_bench_reference_arm_prints_the_contract_line():
     assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and "sample" in cb
     assert d["e2e"] == {"value": d["value"], "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert d["gpu_launches"] == 0
+
+
+def test_nvls_form_policy_is_a_pure_function_of_group_and_bytes():
+    """NvlsAllReduce.choose_form / pays / form_fits (ops.py) decide on (world, message bytes) only, so every rank picks
+    the same form without talking: flag-in-data forms for small messages, in-switch reduction beyond ~1 MB, and at TP2
+    the fused launch only pays up to 1 MB (profiles/r2c_bench_n2.jsonl: peer-store + norm kernel 19.0 us vs fused 21.3 us
+    at 2 MB; at world 8 fused two-shot 27.3 us vs 34.8 us)."""
+    from b200attn import ops
+    MB = 1 << 20
+
+    def comm(world):
+        c = object.__new__(ops.NvlsAllReduce)
+        c.world, c.max_bytes, c.ll_max_bytes = world, 8 * MB, 4 * MB
+        c.ll1_budget, c.ll2_max, c.one_shot_budget, c.fused_max_pair, c.forced_form = MB, MB, 3 << 19, MB, None
+        return c
+
+    for world in (2, 4, 8):
+        c = comm(world)
+        forms = [c.choose_form(n) for n in (4096, 64 * 1024, 512 * 1024, 2 * MB, 4 * MB)]
+        assert forms == [comm(world).choose_form(n) for n in (4096, 64 * 1024, 512 * 1024, 2 * MB, 4 * MB)]
+        assert forms[0] == 2                                        # tiny: LL one-shot, no barrier
+        assert forms[2] == 3                                        # <= 1 MB: LL two-shot
+        assert forms[3] in (0, 1) and forms[4] in (0, 1)            # beyond: the switch reduces
+        for n, f in zip((4096, 64 * 1024, 512 * 1024, 2 * MB, 4 * MB), forms):
+            assert c.form_fits(f, n)
+    assert comm(8).choose_form(2 * MB) == 0 and comm(2).choose_form(2 * MB) == 1   # world 8: reduce-scatter + all-gather
+    x2 = type("T", (), {})()
+    for world, nbytes, want in ((2, 512 * 1024, True), (2, 2 * MB, False), (4, 2 * MB, True), (8, 4 * MB, True)):
+        c = comm(world)
+        c.fits = lambda x: True
+        x2.numel = lambda n=nbytes: n // 2
+        assert c.pays(x2) is want
