@@ -41,6 +41,7 @@ extern "C" {
 #define B200_ERR_WORKSPACE (-4)  /* workspace too small for (batch, heads, splits) */
 #define B200_ERR_RANGE (-5)      /* negative or overflowing count */
 #define B200_ERR_UNAVAILABLE (-6)/* requested kernel variant not built / no driver entry point */
+#define B200_ERR_SCRATCH_LIMIT (-7) /* problem needs more than the library's built-in scratch array */
 
 int b200_version(void);
 const char* b200_status_string(int status);
@@ -155,6 +156,37 @@ int b200_attn_decode(const void* q, int64_t q_token_stride,
                      int32_t head_dim, int32_t page_size, float softmax_scale,
                      int32_t num_splits, void* workspace, size_t workspace_bytes,
                      void* stream);
+
+/* (3, no-allocation form) The same paged decode for a caller that has no device memory to give as workspace.
+ *     No counterpart in the reference: there, flash-attn asks torch's caching allocator for its split
+ *     accumulators on every call, which a torch-free host cannot do.  This entry point is for the callers of
+ *     THIS library that cannot allocate: an engine that has already turned all free HBM into KV cache and can no
+ *     longer rely on cudaMalloc succeeding; a cgo / JNI / plain-ctypes binding that owns no device allocator;
+ *     a request loop that cannot afford the device-wide stall of cudaMalloc / cudaFree.
+ *     Arguments and results are those of b200_attn_decode minus (workspace, workspace_bytes).  The split-K
+ *     scratch is an array of B200_DECODE_STATIC_SCRATCH_BYTES (8 MiB) built into the library: every GPU the
+ *     library is loaded on holds those bytes until the process exits, whether or not this function is called.
+ *     Limits and rules:
+ *       - b200_decode_workspace_bytes(batch, num_heads, num_splits) must be <= B200_DECODE_STATIC_SCRATCH_BYTES,
+ *         else B200_ERR_SCRATCH_LIMIT is returned and nothing is launched (lower num_splits, or use
+ *         b200_attn_decode with your own workspace).  num_splits == 1 uses no scratch and always fits.
+ *       - The function itself allocates and frees nothing (no cudaMalloc/cudaFree, no allocating library call).
+ *       - The first call on each device looks up that device's address of the array (cudaGetSymbolAddress, with
+ *         the device current) and opts the kernel into its shared-memory size.  Make that first call outside any
+ *         stream capture.
+ *       - All calls on a device share the one array, and it keeps the previous call's contents.  Each call
+ *         clears the arrival tickets it is about to use (a small stream-ordered memset); everything else is
+ *         overwritten before it is read.  Two calls whose GPU work can overlap (different streams without an
+ *         ordering between them, or two host threads) race on the array and give wrong results: order them. */
+#define B200_DECODE_STATIC_SCRATCH_BYTES (8 * 1024 * 1024)
+int b200_attn_decode_static_scratch(const void* q, int64_t q_token_stride,
+                                    const void* k_cache, const void* v_cache,
+                                    void* out, int64_t out_token_stride,
+                                    const int32_t* context_lens,
+                                    const int32_t* block_tables, int32_t bt_row_stride,
+                                    int32_t batch, int32_t num_heads, int32_t num_kv_heads,
+                                    int32_t head_dim, int32_t page_size, float softmax_scale,
+                                    int32_t num_splits, void* stream);
 
 /* ---------------------------------------------------------------------------------
  * (2) Varlen causal prefill / chunked-prefill attention.  Replaces

@@ -33,6 +33,9 @@ SIGNATURES = {
     "b200_attn_decode": (c_int32, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p,
                                    c_void_p, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, c_float,
                                    c_int32, c_void_p, c_size_t, c_void_p]),
+    "b200_attn_decode_static_scratch": (c_int32, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p,
+                                                  c_void_p, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32,
+                                                  c_float, c_int32, c_void_p]),
     "b200_attn_prefill": (c_int32, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_int64,
                                     c_void_p, c_void_p, c_void_p, c_int32, c_int32, c_int32, c_int32, c_int32,
                                     c_int32, c_int32, c_int32, c_int32, c_int64, c_float, c_int32, c_void_p]),

@@ -66,6 +66,9 @@ const char* b200_status_string(int status) {
         case B200_ERR_WORKSPACE: return "b200attn: split-K workspace too small";
         case B200_ERR_RANGE: return "b200attn: negative or out-of-range count";
         case B200_ERR_UNAVAILABLE: return "b200attn: requested kernel variant unavailable";
+        case B200_ERR_SCRATCH_LIMIT:
+            return "b200attn: batch x heads x splits needs more than the 8 MiB built-in scratch "
+                   "(B200_DECODE_STATIC_SCRATCH_BYTES); lower num_splits or pass your own workspace to b200_attn_decode";
         default: break;
     }
     if (status > 0) return cudaGetErrorString(static_cast<cudaError_t>(status));

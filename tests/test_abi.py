@@ -41,7 +41,7 @@ def test_header_symbols_all_exported_and_bound(lib):
 def test_version_and_status_strings(lib):
     assert lib.b200_version() == 100
     assert lib.b200_status_string(0) == b"ok"
-    for code in range(-6, 0):
+    for code in range(-7, 0):
         assert lib.b200_status_string(code).startswith(b"b200attn:")
 
 
@@ -54,6 +54,10 @@ def test_argument_errors_without_gpu(lib):
     assert lib.b200_attn_decode(16, 128, 16, 16, 16, 128, 16, 16, 4, 2, 6, 4, 128, 256, 1.0, 1, None, 0, None) == -2
     assert lib.b200_attn_decode(16, 128, 16, 16, 16, 128, 16, 16, 4, 2, 8, 4, 128, 256, 1.0, 4, None, 0, None) == -4
     assert lib.b200_silu_and_mul(16, 16, 3, 100, None) == -2
+    # the no-allocation decode refuses, before touching CUDA, what its built-in 8 MiB scratch cannot hold
+    assert lib.b200_decode_workspace_bytes(16, 32, 64) > 8 * 1024 * 1024
+    assert lib.b200_attn_decode_static_scratch(16, 128, 16, 16, 16, 128, 16, 16, 4, 16, 32, 8, 128, 256, 1.0, 64, None) == -7
+    assert lib.b200_attn_decode_static_scratch(16, 128, 16, 16, 16, 128, 16, 16, 4, 2, 6, 4, 128, 256, 1.0, 1, None) == -2
 
 
 def test_decode_plan_is_static_and_bounded(lib):
