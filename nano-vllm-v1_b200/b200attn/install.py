@@ -66,8 +66,9 @@ def _rmsnorm_forward(self, x, residual=None):
         return ops.rms_norm(x if x.is_contiguous() else x.contiguous(), self.weight, self.eps)
     # x may be the un-reduced output of the RowParallelLinear in front (ops.tp_row_parallel_output): the
     # all-reduce then runs inside this launch
-    return ops.tp_add_rms_norm(x if x.is_contiguous() else x.contiguous(), residual if residual.is_contiguous() else residual.contiguous(),
-                               self.weight, self.eps)
+    # No .contiguous() here: a copy taken before a pending all-reduce has run would hold un-reduced partial sums
+    # (ADVICE r2).  tp_add_rms_norm settles the pending sum first and only then makes its inputs contiguous.
+    return ops.tp_add_rms_norm(x, residual, self.weight, self.eps)
 
 
 def _qwen3_model_forward(self, input_ids, positions, _reference_forward=None):

@@ -653,10 +653,16 @@ def tp_add_rms_norm(x: torch.Tensor, residual: Optional[torch.Tensor], weight: t
     all-reduce happens inside the same launch."""
     global _PENDING
     if _PENDING is not None:
-        if _PENDING is x and residual is not None:
+        if _PENDING is x and residual is not None and x.is_contiguous() and residual.is_contiguous():
             _PENDING = None
             return _TP_NVLS.all_reduce_add_rms_norm(x, residual, weight, eps)
+        # x is something else -- possibly a VIEW of the pending tensor: reduce the original in place first, so
+        # that whatever copy is made below reads reduced sums
         flush_pending_all_reduce()
+    if not x.is_contiguous():
+        x = x.contiguous()
+    if residual is not None and not residual.is_contiguous():
+        residual = residual.contiguous()
     return rms_norm(x, weight, eps, residual)
 
 

@@ -279,3 +279,44 @@ def test_nvls_form_policy_is_a_pure_function_of_group_and_bytes():
         c.fits = lambda x: True
         x2.numel = lambda n=nbytes: n // 2
         assert c.pays(x2) is want
+
+
+def test_pending_all_reduce_is_settled_before_any_copy_of_its_tensor(monkeypatch):
+    """RMSNorm.forward may be handed a NON-contiguous view of the RowParallelLinear output whose
+    all-reduce was deferred.  The reduce must hit the original BEFORE the view is copied, or the norm would run on
+    un-reduced partial sums (reference order: dist.all_reduce at layers/linear.py:407-410, then layernorm.py:95-141).
+    Host logic only: the collective and the norm kernel are replaced by recording stand-ins."""
+    import torch
+    from b200attn import install, ops
+    log = []
+
+    def fake_all_reduce(t):
+        log.append("reduce")
+        t.mul_(2)                                   # "sum over 2 ranks" of identical partials
+        return t
+
+    def fake_rms_norm(x, weight, eps, residual=None):
+        assert x.is_contiguous() and (residual is None or residual.is_contiguous())
+        log.append("norm")
+        return x.clone(), residual
+
+    monkeypatch.setattr(ops, "tp_all_reduce_", fake_all_reduce)
+    monkeypatch.setattr(ops, "rms_norm", fake_rms_norm)
+    y = torch.ones(4, 16)                           # un-reduced partial sums, pending
+    monkeypatch.setattr(ops, "_PENDING", y)
+    view = y[:, ::2]                                # what a model that slices between o_proj and the norm would pass
+    assert not view.is_contiguous()
+
+    class Norm:
+        weight, eps = torch.ones(8), 1e-6
+
+    out, _ = install._rmsnorm_forward(Norm(), view, torch.zeros(4, 8))
+    assert log == ["reduce", "norm"]
+    assert ops._PENDING is None
+    assert torch.equal(out, torch.full((4, 8), 2.0))          # the norm saw the REDUCED values
+    # same for the residual-free form
+    log.clear()
+    y2 = torch.ones(4, 16)
+    monkeypatch.setattr(ops, "_PENDING", y2)
+    out2 = install._rmsnorm_forward(Norm(), y2[:, ::2])
+    assert log == ["reduce", "norm"] and torch.equal(out2[0], torch.full((4, 8), 2.0))
