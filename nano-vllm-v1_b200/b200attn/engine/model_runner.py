@@ -180,6 +180,10 @@ def run(self, seqs, _get_context, _reset_context):
     temperatures = self.prepare_sample(seqs) if self.rank == 0 else None
     logits = self.run_model(input_ids, positions)
     token_ids = self.sampler(logits, temperatures).tolist() if self.rank == 0 else None
+    if self.rank == 0 and self.world_size > 1:
+        # .tolist() has just synchronised the device: the cheapest place to learn that an all-reduce kernel of this
+        # step gave up on a stalled peer, before its garbage becomes tokens (workers report at shutdown)
+        ops.raise_if_collectives_failed()
     need = self._b200_need_logits_host
     if need is None:                                       # prepare_model_input was not ours
         need = _get_context().seq_need_compute_logits
@@ -261,8 +265,15 @@ def call(self, method_name, *args, _reference_call=None):
         if self.rank == 0 and self.world_size > 1:
             self.write_shm("exit")                         # workers first: the tear-down below is collective
         try:
-            ops.shutdown_collectives()                     # b200_ar_destroy / b200_nvls_destroy, before the group goes
-            return self.exit()
+            late_error = None
+            try:
+                ops.shutdown_collectives()                 # b200_ar_destroy / b200_nvls_destroy, before the group goes
+            except RuntimeError as exc:                    # a collective had timed out: finish the tear-down, then say so
+                late_error = exc
+            result = self.exit()
+            if late_error is not None:
+                raise late_error
+            return result
         finally:
             release_side_arena(self)
     return _reference_call(self, method_name, *args)

@@ -666,6 +666,27 @@ def tp_add_rms_norm(x: torch.Tensor, residual: Optional[torch.Tensor], weight: t
     return rms_norm(x, weight, eps, residual)
 
 
+def collectives_status() -> int:
+    """Worst status word of the live peer-memory communicators: 0 = healthy, 1 = some wait inside a launch gave up
+    after B200ATTN_AR_TIMEOUT_S (b200_ar_status / b200_nvls_status).  Costs one 4-byte device->host copy per
+    communicator, so call it where the host has just synchronised anyway."""
+    worst = 0
+    for c in (_TP_AR, _TP_NVLS):
+        if c not in (None, False):
+            worst = max(worst, int(c.status()))
+    return worst
+
+
+def raise_if_collectives_failed() -> None:
+    """After a timeout the barrier and packet epochs of the ranks no longer agree, and every later all-reduce or
+    fused norm returns garbage: turn that into an exception instead of wrong tokens.  The reference's
+    NCCL path would abort the process in the same situation (watchdog, linear.py:407-410's dist.all_reduce)."""
+    if collectives_status() != 0:
+        raise RuntimeError("b200attn: a tensor-parallel all-reduce kernel timed out waiting for a peer rank "
+                           "(B200ATTN_AR_TIMEOUT_S); every result since then is invalid -- restart the engine "
+                           "(B200ATTN_ALLREDUCE=0 B200ATTN_NVLS=0 keeps the collectives on NCCL)")
+
+
 def shutdown_collectives() -> None:
     """Tear the peer-memory communicators down (b200_ar_destroy / b200_nvls_destroy) before the reference
     destroys its process group (ModelRunner.exit, model_runner.py:187-193).  Collective: every rank calls it."""
@@ -678,6 +699,10 @@ def shutdown_collectives() -> None:
     torch.cuda.synchronize()
     if dist.is_initialized() and dist.get_world_size() > 1:
         dist.barrier()                              # no rank is still inside a call that reads this rank's buffer
+    failed = any(int(c.status()) != 0 for c in live)
     for c in live:
         c.destroy()
     _TP_AR = _TP_NVLS = None
+    if failed:                                      # workers have no per-step check: this is where they report
+        raise RuntimeError("b200attn: a tensor-parallel all-reduce kernel had timed out before shutdown "
+                           "(B200ATTN_AR_TIMEOUT_S); results of this process after that point were invalid")

@@ -320,3 +320,34 @@ def test_pending_all_reduce_is_settled_before_any_copy_of_its_tensor(monkeypatch
     monkeypatch.setattr(ops, "_PENDING", y2)
     out2 = install._rmsnorm_forward(Norm(), y2[:, ::2])
     assert log == ["reduce", "norm"] and torch.equal(out2[0], torch.full((4, 8), 2.0))
+
+
+def test_a_timed_out_collective_is_an_exception_not_wrong_tokens(monkeypatch):
+    """after a bounded wait gives up, the status word is sticky and all later all-reduces are garbage.
+    The engine polls it where it has just synchronised (rank 0, after sampling) and at shutdown (every rank)."""
+    from b200attn import ops
+
+    class Comm:
+        def __init__(self, st):
+            self.st, self.destroyed = st, False
+
+        def status(self):
+            return self.st
+
+        def destroy(self):
+            self.destroyed = True
+
+    monkeypatch.setattr(ops, "_TP_AR", Comm(0))
+    monkeypatch.setattr(ops, "_TP_NVLS", False)          # NVLS unavailable on this group
+    assert ops.collectives_status() == 0
+    ops.raise_if_collectives_failed()
+    bad = Comm(1)
+    monkeypatch.setattr(ops, "_TP_NVLS", bad)
+    assert ops.collectives_status() == 1
+    with pytest.raises(RuntimeError, match="timed out"):
+        ops.raise_if_collectives_failed()
+    import torch
+    monkeypatch.setattr(torch.cuda, "synchronize", lambda *a, **k: None)
+    with pytest.raises(RuntimeError, match="timed out"):
+        ops.shutdown_collectives()
+    assert bad.destroyed and ops._TP_AR is None and ops._TP_NVLS is None     # torn down before the error is raised
