@@ -873,15 +873,27 @@ __global__ void __launch_bounds__(ps_threads(WGS), 1) prefill_persist_kernel(
     }
 }
 
-const CUtensorMap* cached_map(const void* base, uint64_t rows, uint64_t heads, uint64_t row_stride_elems, uint32_t box_rows) {
+bool cached_map(CUtensorMap* out, const void* base, uint64_t rows, uint64_t heads, uint64_t row_stride_elems, uint32_t box_rows) {
     static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+    static std::mutex mu;
+    static size_t cap = 0;
+    std::lock_guard<std::mutex> lock(mu);
+    if (cap == 0) {
+        const char* env = getenv("B200ATTN_MAP_CACHE_CAP");     // tests shrink it to force evictions inside one launch
+        const long v = env ? atol(env) : 0;
+        cap = v > 0 ? (size_t)v : 4096;
+    }
     const MapKey key{base, rows, heads, row_stride_elems, box_rows, current_device()};
     auto it = cache.find(key);
-    if (it != cache.end()) return &it->second;
-    if (cache.size() >= 4096) cache.clear();                  // bounded; K/V cache maps are re-encoded on demand
+    if (it != cache.end()) { *out = it->second; return true; }
+    // The q/k/v keys carry total_q (the TMA bound that keeps box loads inside the allocation), so a serving process
+    // keeps minting new keys; when the table is full it is emptied.  Safe at any point: callers hold copies.
+    if (cache.size() >= cap) cache.clear();
     CUtensorMap m;
-    if (!make_map(&m, base, rows, heads, row_stride_elems, box_rows)) return nullptr;
-    return &cache.emplace(key, m).first->second;
+    if (!make_map(&m, base, rows, heads, row_stride_elems, box_rows)) return false;
+    cache.emplace(key, m);
+    *out = m;
+    return true;
 }
 
 static long long* g_trace = nullptr;
@@ -933,19 +945,18 @@ int launch_attn_prefill_persist(const PrefillArgs& a, const int32_t* plan, int32
         emu = v < 0 ? 0 : (v > 4 ? 4 : v);
     }
     const bool paged = a.block_tables != nullptr;
-    const CUtensorMap* pq = cached_map(a.q, (uint64_t)a.total_q, (uint64_t)a.Hq, (uint64_t)a.q_token_stride);
-    const CUtensorMap* pq64 = cached_map(a.q, (uint64_t)a.total_q, (uint64_t)a.Hq, (uint64_t)a.q_token_stride, 64);
-    const CUtensorMap *pk, *pv;
+    CUtensorMap mq, mq64, mk, mv;                                // copies: a later look-up may empty the cache
+    bool ok = cached_map(&mq, a.q, (uint64_t)a.total_q, (uint64_t)a.Hq, (uint64_t)a.q_token_stride) &&
+              cached_map(&mq64, a.q, (uint64_t)a.total_q, (uint64_t)a.Hq, (uint64_t)a.q_token_stride, 64);
     if (paged) {
         const uint64_t rows = (uint64_t)a.num_cache_blocks * B200_PAGE;
-        pk = cached_map(a.k, rows, (uint64_t)a.Hkv, (uint64_t)a.Hkv * B200_HD);
-        pv = cached_map(a.v, rows, (uint64_t)a.Hkv, (uint64_t)a.Hkv * B200_HD);
+        ok = ok && cached_map(&mk, a.k, rows, (uint64_t)a.Hkv, (uint64_t)a.Hkv * B200_HD) &&
+             cached_map(&mv, a.v, rows, (uint64_t)a.Hkv, (uint64_t)a.Hkv * B200_HD);
     } else {
-        pk = cached_map(a.k, (uint64_t)a.total_q, (uint64_t)a.Hkv, (uint64_t)a.k_token_stride);
-        pv = cached_map(a.v, (uint64_t)a.total_q, (uint64_t)a.Hkv, (uint64_t)a.v_token_stride);
+        ok = ok && cached_map(&mk, a.k, (uint64_t)a.total_q, (uint64_t)a.Hkv, (uint64_t)a.k_token_stride) &&
+             cached_map(&mv, a.v, (uint64_t)a.total_q, (uint64_t)a.Hkv, (uint64_t)a.v_token_stride);
     }
-    if (!pq || !pk || !pv || !pq64) return -6;
-    const CUtensorMap &mq = *pq, &mk = *pk, &mv = *pv, &mq64 = *pq64;
+    if (!ok) return -6;
     PersistParams p;
     p.cu_q = a.cu_q; p.cu_k = a.cu_k; p.block_tables = a.block_tables; p.bt_row_stride = a.bt_row_stride;
     p.out = (__nv_bfloat16*)a.out; p.out_token_stride = a.out_token_stride;

@@ -3,6 +3,7 @@
 #pragma once
 #include <cuda.h>
 
+#include <mutex>
 #include <unordered_map>
 
 #include "common.cuh"
@@ -193,8 +194,8 @@ static inline bool make_map(CUtensorMap* m, const void* base, uint64_t rows, uin
 // Tensor maps are a pure function of (base, rows, heads, row stride): encode each one ONCE and reuse it
 // ("encoded on the host once per (cache pointer, Hkv)").  The K/V cache maps of every
 // layer and the handful of q/k/v addresses the caching allocator hands out recur on every step; a step then
-// costs three hash lookups instead of three cuTensorMapEncodeTiled driver calls.  Per process, one Python
-// thread per GPU process (the reference's model), bounded size.
+// costs four hash lookups instead of four cuTensorMapEncodeTiled driver calls.  Per process, mutex-guarded,
+// bounded size (B200ATTN_MAP_CACHE_CAP entries, default 4096; when full it is emptied and refills on demand).
 struct MapKey {
     const void* base; uint64_t rows, heads, stride; uint32_t box_rows; int dev;
     bool operator==(const MapKey& o) const {
@@ -209,7 +210,8 @@ struct MapKeyHash {
         return (size_t)(h ^ (h >> 29));
     }
 };
-const CUtensorMap* cached_map(const void* base, uint64_t rows, uint64_t heads, uint64_t row_stride_elems,
-                              uint32_t box_rows = 128);   // attn_prefill_persist.cu
+// Copies the map OUT (by value): the cache may evict on any later look-up, so no caller ever holds a pointer into it.
+bool cached_map(CUtensorMap* out, const void* base, uint64_t rows, uint64_t heads, uint64_t row_stride_elems,
+                uint32_t box_rows = 128);                 // attn_prefill_persist.cu
 
 }  // namespace b200

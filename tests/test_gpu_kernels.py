@@ -728,7 +728,10 @@ def test_decode_full_size_cfg3_tp_shapes(ops, Hq, Hkv):
 
 
 @pytest.mark.parametrize("env", [{"B200ATTN_PREFILL_WGS": "2"}, {"B200ATTN_PREFILL_EMU": "1"}, {"B200ATTN_PREFILL_WGS": "2", "B200ATTN_PREFILL_EMU": "2"},
-                                 {"B200ATTN_DECODE_FUSED_REDUCE": "0", "B200ATTN_DECODE_SPLITS": "3"}])
+                                 {"B200ATTN_DECODE_FUSED_REDUCE": "0", "B200ATTN_DECODE_SPLITS": "3"},
+                                 # tensor-map cache of 3 entries: the 4th look-up of EVERY prefill launch empties it while the
+                                 # first three maps are in use (they used to be pointers into the cache)
+                                 {"B200ATTN_MAP_CACHE_CAP": "3"}, {"B200ATTN_MAP_CACHE_CAP": "1"}])
 def test_measured_and_not_adopted_variants_still_match_the_oracle(env):
     """The A/B knobs kept in the shipped library (two softmax warpgroups per query tile, polynomial exp2, the separate
     reduce launch) are read once per process, so each runs in a subprocess: a mixed paged batch (prefill rows through the
