@@ -251,7 +251,7 @@ def run_ours(args):
     # `value`: the step replayed from a CUDA graph -- how the engine runs this very call (ModelRunner.capture_cudagraph /
     # run_model replay, model_runner.py:568-600,640-715: graph-form decode, row a6/a13); the eager launches of the same
     # step are timed next to it and reported as `eager_ms_per_step`.
-    launch_mode = "cuda-graph replay (ModelRunner's decode form)"
+    launch_mode = "cuda-graph replay"
     try:
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
@@ -267,9 +267,18 @@ def run_ours(args):
     except Exception as e:                                      # noqa: BLE001
         launch_mode = f"eager launches (graph capture failed: {type(e).__name__})"
         step_timed = step_resident
+    # one region of K = 20 steps lasts ~23 ms, and `value` / `e2e` moved by 1.4 % / 4 % between two boxes.
+    # Each figure is now the MEDIAN over REGIONS regions of exactly K steps, every region bracketed by barrier + synchronize
+    # (max over ranks per region) as the contract asks; `timed_regions` in the line says so.
+    REGIONS = 9
+
+    def timed_median(fn, steps):
+        import statistics
+        return statistics.median(timed(fn, steps) for _ in range(REGIONS))
+
     ms_eager = timed(step_resident, args.steps)
-    ms_total = timed(step_timed, args.steps)
-    ms_e2e = timed(step_e2e, args.steps)
+    ms_total = timed_median(step_timed, args.steps)
+    ms_e2e = timed_median(step_e2e, args.steps)
     clocks = sampler.finish()                                  # covers both timed regions (resident + e2e)
 
     # dominant kernel alone (paged_decode_kernel [+ reduce when split]) on the launching stream
@@ -296,6 +305,11 @@ def run_ours(args):
     if not args.no_gpu_baseline:
         mine = gpu_baseline_leg(rank, world, local, args)
         ms_ref = float(mine.get("ms_per_step", 0.0)) if "ms_per_step" in mine else -1.0
+        ms_ref_eager = ms_ref
+        # this repo's step is a graph replay, so the reference gets the better of its eager and its
+        # graph-replayed time (tools/ref_attention_bench.py times both)
+        if mine.get("ms_per_step_graph") and 0 < float(mine["ms_per_step_graph"]) < ms_ref:
+            ms_ref = float(mine["ms_per_step_graph"])
         if world > 1:
             t = torch.tensor([ms_ref, -ms_ref], device=device, dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -305,6 +319,7 @@ def run_ours(args):
             ref_value = total_bytes / (ms_ref * 1e-3) / 1e9
             gpu_base = {"impl": mine.get("impl"), "flash_attn": mine.get("flash_attn"), "value": round(ref_value, 1),
                         "unit": "GB/s", "ms_per_step": round(ms_ref, 4), "speedup": round(value / ref_value, 3),
+                        "ms_per_step_eager_rank0": round(ms_ref_eager, 4), "ms_per_step_graph_rank0": mine.get("ms_per_step_graph"),
                         "how": "same seeded tensors, same step (scatter + paged decode of one layer), subprocess per rank, "
                                "CUDA events, max over ranks"}
         else:
@@ -325,10 +340,10 @@ def run_ours(args):
         "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": WORKLOAD, "batch": B, "context_len": CTX, "q_heads": HQ, "kv_heads": HKV,
                    "head_dim": D, "page": PAGE, "sharding": f"tp{world} (heads; no collective on this path)",
-                   "step": "Attention.forward = kv_scatter + paged decode (split merge inside the decode launch)",
+                   "step": "kv_scatter + paged decode",
                    "num_splits": num_splits,
-                   "l2": "inputs larger than L2 (K/V working set %.2f GB per GPU vs 126 MB L2)" % (dec_b / 1e9)},
-        "launch": launch_mode, "eager_ms_per_step": round(ms_eager / args.steps, 4),
+                   "l2": "inputs larger than L2 (%.2f GB per GPU)" % (dec_b / 1e9)},
+        "timed_regions": REGIONS, "launch": launch_mode, "eager_ms_per_step": round(ms_eager / args.steps, 4),
         "e2e": {"value": round(e2e_value, 1), "unit": "GB/s", "h2d_bytes_per_step": h2d * world,
                 "d2h_bytes_per_step": d2h * world, "ms_per_step": round(ms_e2e / args.steps, 4)},
         "gpu_launches": launches_per_step * args.steps,
@@ -350,7 +365,40 @@ def run_ours(args):
         line["tok_per_s"] = tok_per_s_leg(world, local)
     sys.stdout.flush()
     os.dup2(saved_stdout, 1)
-    print(json.dumps(line), flush=True)
+    print(json.dumps(compact_line(line), separators=(",", ":")), flush=True)
+
+
+_PROSE_KEYS = ("timing", "how", "statistic")
+_LAST_KEYS = ("tok_per_s", "gpu_baseline", "prefill", "allreduce")
+
+
+def compact_line(line):
+    """the driver keeps only the tail of the line, so (a) explanatory strings stay in DESIGN.md section 5
+    instead of riding in every line, (b) per-form all-reduce records shrink to what is judged (parity flag, worst ulps),
+    (c) the secondary legs come LAST, where a truncated tail still shows them.  Numbers are untouched."""
+    def strip(o):
+        if isinstance(o, dict):
+            d = {k: strip(v) for k, v in o.items() if k not in _PROSE_KEYS}
+            if isinstance(d.get("peak_source"), str):               # which peak: the driver-measured file or the guide's fallback
+                d["peak_source"] = "measured" if d["peak_source"].startswith("measured") else "fallback"
+            return d
+        if isinstance(o, list):
+            return [strip(v) for v in o]
+        return o
+
+    out = strip(line)
+    ar = out.get("allreduce")
+    if isinstance(ar, dict):
+        for k, v in list(ar.items()):
+            if isinstance(v, dict) and k.startswith("nvls_fused_") and "parity_ok" in v:
+                ar[k] = {"parity_ok": v["parity_ok"], "ulps": v.get("normed_max_ulps_vs_add_rms_of_sum"),
+                         "same": round(v.get("normed_identical_fraction", 0.0), 5), "status": v.get("status")}
+        pm = ar.get("peer_memory")
+        if isinstance(pm, dict):
+            ar["peer_memory"] = {k: pm[k] for k in ("parity_ok", "form", "max_abs_diff_vs_nccl") if k in pm}
+    head = {k: v for k, v in out.items() if k not in _LAST_KEYS}
+    head.update({k: out[k] for k in _LAST_KEYS if k in out})
+    return head
 
 
 def _clean_env():
@@ -509,6 +557,30 @@ def allreduce_leg(ops, device, rank, world, timed, tokens=256, hidden=4096, call
                                     "residual_bit_equal_to_add_rms_of_sum": req, "normed_max_ulps_vs_add_rms_of_sum": uy,
                                     "status": nv.status()}
             res["nvls_default_form"] = names[nv.choose_form(x.numel() * 2)]
+            # the forms the engine's policy picks for DECODE-sized messages (T = 1..64 rows) at this world
+            # size, checked like the 2 MB message above -- every form that fits plus the default, first T rows of x
+            sweep = {"tokens": [1, 2, 8, 16, 64], "checked": 0, "failed": [], "default_form": {}}
+            for T in sweep["tokens"]:
+                xs, rs = x[:T].contiguous(), resid[:T].contiguous()
+                sweep["default_form"][str(T)] = nv.choose_form(xs.numel() * 2)
+                for form in (0, 1, 2, 3):
+                    if not nv.form_fits(form, xs.numel() * 2):
+                        continue
+                    plain = nv.all_reduce_add_rms_norm(xs, None, None, 0.0, form=form)
+                    d = (plain.double() - exact64[:T]).abs()
+                    ok = bool((d <= (tol_switch if form < 2 else tol)[:T]).all().item()) and same_on_all_ranks(plain)
+                    if form >= 2:
+                        ok = ok and bool(torch.equal(plain, once[:T]))
+                    want_y, want_r = ops.rms_norm(plain.clone(), w, 1e-6, rs.clone())
+                    r2 = rs.clone()
+                    y, _ = nv.all_reduce_add_rms_norm(xs, r2, w, 1e-6, form=form)
+                    ok = (ok and bool(torch.equal(r2, want_r)) and ulps(y, want_y) <= 2.0 and same_on_all_ranks(y)
+                          and same_on_all_ranks(r2))
+                    sweep["checked"] += 1
+                    if not ok:
+                        sweep["failed"].append([T, form])
+            sweep["parity_ok"] = bool(not sweep["failed"] and sweep["checked"] > 0 and nv.status() == 0)
+            res["nvls_decode_sizes"] = sweep
         else:
             res["nvls_fused"] = {"unavailable": "no NVLS multicast mapping for this group (peer-store form in use)"}
 
@@ -537,7 +609,7 @@ def allreduce_leg(ops, device, rank, world, timed, tokens=256, hidden=4096, call
         res["us_per_call_graph_replay"] = {k: round(v, 2) for k, v in lat.items()}
         res["status_after"] = {"peer_memory": ops._TP_AR.status() if ops._TP_AR else None, "nvls": nv.status() if nv else None}
         res["parity_ok"] = bool(peer_ok and all(v.get("parity_ok", True) for k, v in res.items()
-                                                if isinstance(v, dict) and k.startswith("nvls_fused_"))
+                                                if isinstance(v, dict) and k.startswith(("nvls_fused_", "nvls_decode_sizes")))
                                 and not any(res["status_after"].values()))
     except Exception as exc:                                           # noqa: BLE001 -- the headline line must still print
         res["error"] = f"{type(exc).__name__}: {exc}"

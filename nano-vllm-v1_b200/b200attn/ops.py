@@ -472,7 +472,10 @@ class NvlsAllReduce:
     symmetric buffer and its multicast mapping come from torch.distributed._symmetric_memory on the reference's
     own process group (plumbing only: cuMemCreate / cuMulticast* and the handle exchange)."""
 
-    def __init__(self, group, max_bytes: int, device=None):
+    def __init__(self, group, max_bytes: int, device=None, group_barrier: bool = True):
+        """group_barrier=False: the caller runs the group-wide synchronisation that must follow b200_nvls_create on
+        every rank itself (tp_nvls folds it into its agreement all-reduce, so a rank whose set-up threw is not left
+        facing its peers' barrier with a different collective)."""
         import ctypes
         import torch.distributed as dist
         lib = load_library()
@@ -507,7 +510,7 @@ class NvlsAllReduce:
         self.one_shot_budget = int(env.get("B200ATTN_NVLS_ONE_SHOT_BUDGET", 3 << 19))
         self.fused_max_pair = int(env.get("B200ATTN_NVLS_FUSED_MAX_TP2", 1 << 20))
         self.forced_form = int(env["B200ATTN_NVLS_FORM"]) if "B200ATTN_NVLS_FORM" in env else None
-        if self.world > 1:
+        if self.world > 1 and group_barrier:
             dist.barrier(group)            # every rank zeroed its buffer before anyone can write into it (b200attn.h)
 
     def choose_form(self, nbytes: int) -> int:
@@ -533,7 +536,7 @@ class NvlsAllReduce:
 
     def pays(self, x: torch.Tensor) -> bool:
         """Whether deferring RowParallelLinear's all-reduce of `x` into the RMSNorm launch beats the peer-memory
-        all-reduce followed by the RMSNorm kernel.  Measured (profiles/r2_nvls_tp2.json, r2_nvls_tp8.json): always at
+        all-reduce followed by the RMSNorm kernel.  Measured (profiles/r2_nvls_tp2.json, r3_nvls_tp4.json, r3_nvls_tp8.json): always at
         TP8 (1.2-2.2x up to 4 MB); with two ranks only up to ~1 MB -- beyond, one posted peer store of the whole
         message beats the round trips of multimem.ld_reduce."""
         return self.fits(x) and (self.world > 2 or x.numel() * 2 <= self.fused_max_pair)
@@ -596,17 +599,23 @@ def tp_nvls():
         if os.environ.get("B200ATTN_NVLS", "1") != "0" and dist.is_initialized() and 1 < dist.get_world_size() <= 8:
             ok = 1
             try:
-                comm = NvlsAllReduce(dist.group.WORLD, int(os.environ.get("B200ATTN_NVLS_MAX_BYTES", NVLS_DEFAULT_MAX_BYTES)))
+                comm = NvlsAllReduce(dist.group.WORLD, int(os.environ.get("B200ATTN_NVLS_MAX_BYTES", NVLS_DEFAULT_MAX_BYTES)),
+                                     group_barrier=False)
             except Exception as exc:                            # noqa: BLE001 -- any set-up failure means "unavailable"
                 comm, ok = None, 0
-                if dist.get_rank() == 0:
-                    print(f"b200attn: NVLS fused all-reduce unavailable ({type(exc).__name__}: {exc}); "
-                          "using the peer-store all-reduce + RMSNorm kernels", flush=True)
-            # all ranks must agree, or some would defer their all-reduce and others not
+                print(f"b200attn[rank {dist.get_rank()}]: NVLS fused all-reduce unavailable ({type(exc).__name__}: {exc}); "
+                      "using the peer-store all-reduce + RMSNorm kernels", flush=True)
+            # The FIRST collective after the try block, on success and on failure alike (a rank that threw
+            # must not meet its peers' barrier with an all-reduce).  It does two jobs: all ranks must agree, or some
+            # would defer their all-reduce and others not; and it is the group-wide synchronisation after
+            # b200_nvls_create -- the buffer was zeroed on the legacy default stream this all-reduce is ordered behind,
+            # and .item() returns only once every rank has contributed.
             flag = torch.tensor([ok], device="cuda", dtype=torch.int32)
             dist.all_reduce(flag, op=dist.ReduceOp.MIN)
             if int(flag.item()) == 1:
                 _TP_NVLS = comm
+            elif comm is not None:
+                comm.destroy()
     return _TP_NVLS
 
 

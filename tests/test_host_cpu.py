@@ -95,6 +95,7 @@ def test_run_returns_host_indices_for_the_untouched_postprocess():
 
     class FakeRunner:
         rank = 0
+        world_size = 1
 
         def prepare_model_input(self, seqs):
             self._b200_need_logits_host = [0, 2]

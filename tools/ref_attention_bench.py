@@ -59,11 +59,34 @@ def main():
             step()
         e1.record()
         torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / a.steps
+        # The same steps replayed from ONE CUDA graph, the way the reference engine itself runs decode
+        # (engine/model_runner.py:640-715) and the way bench.py times this repo's step: no per-step Python / launch cost.
+        ms_graph = None
+        try:
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                step()
+            torch.cuda.current_stream().wait_stream(side)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                for _ in range(a.steps):
+                    step()
+            graph.replay()
+            torch.cuda.synchronize()
+            e0.record()
+            graph.replay()
+            e1.record()
+            torch.cuda.synchronize()
+            ms_graph = e0.elapsed_time(e1) / a.steps
+        except Exception as exc:                                   # noqa: BLE001 -- the eager number still stands
+            ms_graph_error = f"{type(exc).__name__}: {exc}"[:200]
     reset_context()
-    ms = e0.elapsed_time(e1) / a.steps
     dec_b, sc_b = bench.algorithmic_bytes(bench.B, bench.CTX, hq, hkv)
     print(json.dumps({"impl": "reference Attention.forward (Triton store_kvcache + flash_attn_with_kvcache)",
                       "flash_attn": flash_attn.__version__, "ms_per_step": round(ms, 4),
+                      "ms_per_step_graph": round(ms_graph, 4) if ms_graph else None,
                       "gbps_per_gpu": round((dec_b + sc_b) / (ms * 1e-3) / 1e9, 1), "rank": a.rank, "world": a.world}))
     return 0
 
