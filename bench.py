@@ -368,7 +368,7 @@ def run_ours(args):
     print(json.dumps(compact_line(line), separators=(",", ":")), flush=True)
 
 
-_PROSE_KEYS = ("timing", "how", "statistic")
+_PROSE_KEYS = ("timing", "how", "statistic", "seconds_all", "init_seconds", "samples")
 _LAST_KEYS = ("tok_per_s", "gpu_baseline", "prefill", "allreduce")
 
 

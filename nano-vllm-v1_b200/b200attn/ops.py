@@ -536,9 +536,11 @@ class NvlsAllReduce:
 
     def pays(self, x: torch.Tensor) -> bool:
         """Whether deferring RowParallelLinear's all-reduce of `x` into the RMSNorm launch beats the peer-memory
-        all-reduce followed by the RMSNorm kernel.  Measured (profiles/r2_nvls_tp2.json, r3_nvls_tp4.json, r3_nvls_tp8.json): always at
-        TP8 (1.2-2.2x up to 4 MB); with two ranks only up to ~1 MB -- beyond, one posted peer store of the whole
-        message beats the round trips of multimem.ld_reduce."""
+        all-reduce followed by the RMSNorm kernel.  Measured (profiles/r2_nvls_tp2.json, r3_nvls_tp4.json, r3_nvls_tp8.json; us per
+        graph-replayed call, chosen fused form vs peer-store all-reduce + norm kernel): TP8 11.3/17.0 at 8 KB, 16.9/26.6 at
+        512 KB, 28.0/35.8 at 2 MB, 36.4/41.9 at 4 MB (1.15-1.9x); TP4 10.8/16.1 at 8 KB, 13.8/21.1 at 512 KB, a tie at 2 MB
+        (28.1/27.9); with two ranks only up to ~1 MB -- beyond, one posted peer store of the whole message beats the
+        round trips of multimem.ld_reduce."""
         return self.fits(x) and (self.world > 2 or x.numel() * 2 <= self.fused_max_pair)
 
     def fits(self, x: torch.Tensor) -> bool:
